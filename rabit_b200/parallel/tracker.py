@@ -1,0 +1,295 @@
+"""Rendezvous tracker for rabit-b200 workers.
+
+The reference repository does not contain a tracker: it relies on dmlc-core's
+``dmlc_tracker``.  This is an independent implementation of the
+*worker-visible* protocol that ``src/host/comm.cc`` (and the reference's
+``src/allreduce_base.cc:221-438``) speaks, so that both our workers and an
+unmodified reference worker binary can rendezvous here:
+
+* every connection: magic 0xff99 both ways, then rank, world_size, task_id, command
+* ``start`` / ``recover``: the tracker answers with rank, tree parent, world size, the
+  tree neighbours and the ring neighbours, then brokers the peer connections
+* ``print``: one log line; ``shutdown``: the rank is done
+
+Topology: binary heap tree; the ring is a depth-first walk of that tree and ranks are
+relabelled so that the ring is simply ``r -> r + 1 (mod n)`` (the ring collectives
+require that, reference allreduce_base.cc:787-789).  A worker that comes back with a
+``task_id`` the tracker has seen before gets its old rank: that is what makes recovery
+after a kill work.
+"""
+import logging
+import socket
+import struct
+import threading
+import time
+
+MAGIC = 0xFF99
+log = logging.getLogger("rabit.tracker")
+
+
+class _Conn(object):
+    """One accepted worker connection with the wire helpers of the protocol."""
+
+    def __init__(self, sock, addr):
+        self.sock = sock
+        self.host = addr[0]
+        self.rank = -1
+        self.world_size = -1
+        self.task_id = "NULL"
+        self.cmd = ""
+        self.port = -1
+        self.wait_accept = 0
+
+    def recv_all(self, n):
+        chunks = []
+        while n > 0:
+            b = self.sock.recv(n)
+            if not b:
+                raise ConnectionError("worker closed the tracker connection")
+            chunks.append(b)
+            n -= len(b)
+        return b"".join(chunks)
+
+    def recv_int(self):
+        return struct.unpack("@i", self.recv_all(4))[0]
+
+    def send_int(self, v):
+        self.sock.sendall(struct.pack("@i", v))
+
+    def recv_str(self):
+        n = self.recv_int()
+        return self.recv_all(n).decode() if n > 0 else ""
+
+    def send_str(self, s):
+        b = s.encode()
+        self.send_int(len(b))
+        if b:
+            self.sock.sendall(b)
+
+    def handshake(self):
+        magic = self.recv_int()
+        if magic != MAGIC:
+            raise ConnectionError("bad magic %x from %s" % (magic, self.host))
+        self.send_int(MAGIC)
+        self.rank = self.recv_int()
+        self.world_size = self.recv_int()
+        self.task_id = self.recv_str()
+        self.cmd = self.recv_str()
+
+
+def build_topology(n):
+    """Return (tree_neighbours, parent, ring) for ranks relabelled along the ring.
+
+    ``tree_neighbours[r]`` is the list of tree-adjacent ranks of r, ``parent[r]`` its
+    parent (-1 for the root) and ``ring[r] = (prev, next)``.
+    """
+    if n == 1:
+        return {0: []}, {0: -1}, {0: (-1, -1)}
+    children = {i: [c for c in (2 * i + 1, 2 * i + 2) if c < n] for i in range(n)}
+
+    def walk(i):
+        # depth-first; the last child's walk is reversed so that the walk returns close to
+        # where it started and consecutive ring members tend to be tree neighbours
+        order = [i]
+        kids = children[i]
+        for k, c in enumerate(kids):
+            sub = walk(c)
+            if k == len(kids) - 1:
+                sub = sub[::-1]
+            order.extend(sub)
+        return order
+
+    order = walk(0)
+    relabel = {old: new for new, old in enumerate(order)}
+    tree, parent, ring = {}, {}, {}
+    for old in range(n):
+        new = relabel[old]
+        nb = [relabel[c] for c in children[old]]
+        par = -1
+        if old != 0:
+            par = relabel[(old + 1) // 2 - 1]
+            nb.append(par)
+        tree[new] = sorted(nb)
+        parent[new] = par
+        ring[new] = ((new - 1) % n, (new + 1) % n)
+    return tree, parent, ring
+
+
+class Tracker(object):
+    """Accept loop + link broker.  ``start()`` runs it on a daemon thread."""
+
+    def __init__(self, nworker, host="127.0.0.1", port=0, port_end=None, verbose=False):
+        self.nworker = nworker
+        self.sock = socket.socket(socket.AF_INET, socket.SOCK_STREAM)
+        self.sock.setsockopt(socket.SOL_SOCKET, socket.SO_REUSEADDR, 1)
+        if port_end is None:
+            self.sock.bind((host, port))
+        else:
+            for p in range(port, port_end):
+                try:
+                    self.sock.bind((host, p))
+                    break
+                except OSError:
+                    continue
+            else:
+                raise OSError("no free tracker port in [%d, %d)" % (port, port_end))
+        self.sock.listen(256)
+        self.host = host
+        self.port = self.sock.getsockname()[1]
+        self.verbose = verbose
+        self.messages = []          # lines received through "print"
+        self.thread = None
+        self.error = None
+        self.start_time = None
+        self.end_time = None
+
+    # environment a worker needs to find this tracker (the launcher adds task id / attempt)
+    def worker_env(self):
+        return {"DMLC_TRACKER_URI": self.host, "DMLC_TRACKER_PORT": str(self.port),
+                "DMLC_ROLE": "worker", "DMLC_NUM_WORKER": str(self.nworker)}
+
+    def _assign(self, c, rank, tree, parent, ring, wait_conn):
+        """Tell worker c who it is and broker its links (see module docstring)."""
+        n = self.nworker
+        c.rank = rank
+        want = set(tree[rank])
+        prv, nxt = ring[rank]
+        if prv not in (-1, rank):
+            want.add(prv)
+        if nxt not in (-1, rank):
+            want.add(nxt)
+        c.send_int(rank)
+        c.send_int(parent[rank])
+        c.send_int(n)
+        c.send_int(len(tree[rank]))
+        for r in tree[rank]:
+            c.send_int(r)
+        c.send_int(prv if prv != rank else -1)
+        c.send_int(nxt if nxt != rank else -1)
+        dialled = []
+        while True:
+            ngood = c.recv_int()
+            good = set(c.recv_int() for _ in range(ngood))
+            # peers we pointed this worker at that it could not reach are stale (they died while
+            # parked): forget them, their replacement will dial this worker instead
+            for r in dialled:
+                if r not in good:
+                    wait_conn.pop(r, None)
+            bad = want - good
+            dial = [r for r in sorted(bad) if r in wait_conn]
+            c.send_int(len(dial))
+            c.send_int(len(bad) - len(dial))
+            for r in dial:
+                c.send_str(wait_conn[r].host)
+                c.send_int(wait_conn[r].port)
+                c.send_int(r)
+            dialled = dial
+            if c.recv_int() != 0:
+                continue
+            c.port = c.recv_int()
+            for r in dial:
+                wait_conn[r].wait_accept -= 1
+                if wait_conn[r].wait_accept == 0:
+                    del wait_conn[r]
+            c.wait_accept = len(bad) - len(dial)
+            if c.wait_accept > 0:
+                wait_conn[rank] = c
+            return
+
+    def _serve(self):
+        n = self.nworker
+        tree, parent, ring = build_topology(n)
+        job_rank = {}          # task_id -> rank, survives worker restarts
+        shutdown = set()
+        wait_conn = {}         # rank -> conn still expecting accept()s from later arrivals
+        pending = []           # first-time workers waiting for the batch rank assignment
+        todo = list(range(n))  # ranks not handed out yet
+        while len(shutdown) < n:
+            fd, addr = self.sock.accept()
+            c = _Conn(fd, addr)
+            try:
+                c.handshake()
+                if c.cmd == "print":
+                    msg = c.recv_str()
+                    self.messages.append(msg)
+                    log.info(msg.rstrip("\n"))
+                    if self.verbose:
+                        print(msg, end="" if msg.endswith("\n") else "\n", flush=True)
+                    continue
+                if c.cmd == "shutdown":
+                    if c.rank >= 0:
+                        shutdown.add(c.rank)
+                        wait_conn.pop(c.rank, None)
+                    continue
+                if c.cmd not in ("start", "recover"):
+                    raise ConnectionError("unknown tracker command %r" % c.cmd)
+                if self.start_time is None:
+                    self.start_time = time.time()
+                rank = c.rank
+                if rank < 0 and c.task_id != "NULL":
+                    rank = job_rank.get(c.task_id, -1)
+                if rank < 0:
+                    pending.append(c)
+                    if len(pending) == len(todo):
+                        # hand out ranks in one go; sorting by host keeps co-located workers adjacent
+                        pending.sort(key=lambda x: x.host)
+                        for p in pending:
+                            r = todo.pop(0)
+                            if p.task_id != "NULL":
+                                job_rank[p.task_id] = r
+                            self._assign(p, r, tree, parent, ring, wait_conn)
+                            p.sock.close()
+                        pending = []
+                    continue
+                # a restarted worker ("start") or a survivor re-joining ("recover")
+                wait_conn.pop(rank, None)
+                self._assign(c, rank, tree, parent, ring, wait_conn)
+            except (ConnectionError, OSError, struct.error) as e:
+                log.warning("tracker: dropped connection from %s: %s", addr[0], e)
+            finally:
+                if c not in pending:
+                    try:
+                        c.sock.close()
+                    except OSError:
+                        pass
+        self.end_time = time.time()
+
+    def start(self):
+        def run():
+            try:
+                self._serve()
+            except Exception as e:  # pylint: disable=broad-except
+                self.error = e
+                log.error("tracker died: %r", e)
+        self.thread = threading.Thread(target=run, name="rabit-tracker", daemon=True)
+        self.thread.start()
+        return self
+
+    def join(self, timeout=None):
+        self.thread.join(timeout)
+        return not self.thread.is_alive()
+
+    def close(self):
+        try:
+            self.sock.close()
+        except OSError:
+            pass
+
+
+def main():
+    """``python -m rabit_b200.parallel.tracker -n 4`` prints the env and serves one job."""
+    import argparse
+    ap = argparse.ArgumentParser(description=__doc__.split("\n")[0])
+    ap.add_argument("-n", "--num-workers", type=int, required=True)
+    ap.add_argument("--host", default="127.0.0.1")
+    ap.add_argument("--port", type=int, default=9091)
+    args = ap.parse_args()
+    t = Tracker(args.num_workers, args.host, args.port, args.port + 1000, verbose=True)
+    for k, v in sorted(t.worker_env().items()):
+        print("%s=%s" % (k, v), flush=True)
+    t.start()
+    t.join()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,77 @@
+/*!
+ * rabit-b200: what the engines need from the GPU side, as an interface so that the host
+ * layer builds and runs (CPU-only) without CUDA. device_backend.cu implements it on
+ * sm_100a; device_stub.cc is linked instead when the library is built without nvcc.
+ *
+ * No counterpart in the reference (it has no GPU path). The operations mirror the host
+ * primitives of HostComm — allreduce / broadcast / allgather that may FAIL with a Status —
+ * so RobustEngine drives both through the same recovery logic.
+ */
+#ifndef RABIT_SRC_DEVICE_DEVICE_BACKEND_H_
+#define RABIT_SRC_DEVICE_DEVICE_BACKEND_H_
+
+#include <cstddef>
+#include <cstdint>
+#include <string>
+
+#include "../host/comm.h"
+
+namespace rabit {
+namespace engine {
+
+/*! \brief counters the benchmark and tests read back */
+struct DeviceStats {
+  uint64_t kernel_launches = 0;   // kernels of this library launched so far
+  uint64_t fused_consensus_ok = 0;
+  uint64_t fused_consensus_mismatch = 0;
+  uint64_t timeouts = 0;
+  int nvls = 0;                   // multicast path usable
+  int p2p = 0;                    // peer mappings established
+};
+
+class DeviceBackend {
+ public:
+  virtual ~DeviceBackend() {}
+  /*! \brief NULL when not compiled in, no GPU, or cfg.device == "off" */
+  static DeviceBackend *Create(const Config &cfg);
+  /*! \brief does ptr point into CUDA device memory? (false without CUDA) */
+  static bool IsDevicePointer(const void *ptr);
+  static bool Compiled();
+
+  /*!
+   * \brief (re)build the symmetric arena: allocate if needed, exchange handles with all
+   *  peers over comm's ring, map everybody. Collective; called after every rendezvous.
+   */
+  virtual bool Attach(HostComm *comm) = 0;
+  /*! \brief drop peer mappings (before a re-rendezvous) */
+  virtual void Detach() = 0;
+  virtual bool attached() const = 0;
+
+  /*!
+   * \brief in-place allreduce on device memory. `code` is this rank's consensus word
+   *  (proto::Request::Code()); the kernel compares all ranks' codes in its entry barrier
+   *  and returns kMismatch without touching data if they differ.
+   * \param lanes values of dtype per item (1 for built-in types, 2 for a {g,h} pair ...)
+   * \param keep if not NULL, the result is additionally written here (device memory):
+   *   that copy is the rabit result cache entry, fused into the kernel's epilogue
+   */
+  virtual Status Allreduce(void *dptr, size_t count, int dtype, int op, int lanes,
+                           uint32_t code, void *keep) = 0;
+  virtual Status Broadcast(void *dptr, size_t size, int root, uint32_t code, void *keep) = 0;
+  virtual Status Allgather(void *dptr, size_t total, size_t slice_begin, size_t slice_end,
+                           uint32_t code, void *keep) = 0;
+
+  // ---- plain memory services for the engines (staging, result cache) ----
+  virtual void *Alloc(size_t nbytes) = 0;
+  virtual void Free(void *dptr) = 0;
+  virtual void CopyD2H(void *dst, const void *src, size_t nbytes) = 0;
+  virtual void CopyH2D(void *dst, const void *src, size_t nbytes) = 0;
+  virtual void CopyD2D(void *dst, const void *src, size_t nbytes) = 0;
+
+  virtual const DeviceStats &stats() const = 0;
+  virtual std::string Describe() const = 0;
+};
+
+}  // namespace engine
+}  // namespace rabit
+#endif  // RABIT_SRC_DEVICE_DEVICE_BACKEND_H_

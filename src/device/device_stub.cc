@@ -1,0 +1,13 @@
+/*!
+ * rabit-b200: link-time stand-in for the sm_100a backend when the library is built
+ * without nvcc (RABIT_CUDA=0). Every pointer is a host pointer, there is no backend.
+ */
+#include "device_backend.h"
+
+namespace rabit {
+namespace engine {
+DeviceBackend *DeviceBackend::Create(const Config &) { return nullptr; }
+bool DeviceBackend::IsDevicePointer(const void *) { return false; }
+bool DeviceBackend::Compiled() { return false; }
+}  // namespace engine
+}  // namespace rabit

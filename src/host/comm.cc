@@ -1,0 +1,519 @@
+/*!
+ * rabit-b200: host transport implementation. See comm.h for the parity map.
+ */
+#include "comm.h"
+
+#include <algorithm>
+#include <cerrno>
+#include <map>
+
+namespace rabit {
+namespace engine {
+
+namespace {
+/*! \brief handshake cookie of the tracker protocol (reference allreduce_base.h kMagic) */
+const int kTrackerMagic = 0xff99;
+
+Status ErrnoStatus() {
+  switch (errno) {
+    case ECONNRESET: case EPIPE: case ECONNABORTED: case ENOTCONN: case ETIMEDOUT:
+      return Status::kPeerClosed;
+    default:
+      return Status::kSockError;
+  }
+}
+inline bool WouldBlock() { return errno == EAGAIN || errno == EWOULDBLOCK || errno == EINTR; }
+
+/*! \brief one non-blocking recv; *got == 0 with kOk means "nothing yet" */
+Status RecvSome(Link *l, char *p, size_t max, size_t *got) {
+  *got = 0;
+  if (max == 0) return Status::kOk;
+  ssize_t n = l->sock.Recv(p, max);
+  if (n > 0) { *got = static_cast<size_t>(n); return Status::kOk; }
+  if (n == 0) return Status::kPeerClosed;
+  return WouldBlock() ? Status::kOk : ErrnoStatus();
+}
+/*! \brief one non-blocking send */
+Status SendSome(Link *l, const char *p, size_t max, size_t *put) {
+  *put = 0;
+  if (max == 0) return Status::kOk;
+  ssize_t n = l->sock.Send(p, max);
+  if (n >= 0) { *put = static_cast<size_t>(n); return Status::kOk; }
+  return WouldBlock() ? Status::kOk : ErrnoStatus();
+}
+/*! \brief largest multiple of unit that is <= v (at least one unit) */
+inline size_t FloorTo(size_t v, size_t unit) { return std::max(unit, v / unit * unit); }
+}  // namespace
+
+const char *StatusName(Status s) {
+  switch (s) {
+    case Status::kOk: return "ok";
+    case Status::kPeerClosed: return "peer-closed";
+    case Status::kSockError: return "socket-error";
+    case Status::kTimeout: return "device-timeout";
+    case Status::kMismatch: return "consensus-mismatch";
+  }
+  return "?";
+}
+
+HostComm::HostComm() {}
+HostComm::~HostComm() { this->CloseLinks(); }
+
+void HostComm::CloseLinks() {
+  for (Link &l : links_) l.sock.Close();
+  links_.clear();
+  tree_.clear();
+  parent_slot_ = -1;
+  ring_prev_ = ring_next_ = nullptr;
+}
+
+Link *HostComm::FindLink(int r) {
+  for (Link &l : links_) if (l.rank == r) return &l;
+  return nullptr;
+}
+
+// ------------------------------------------------------------------ tracker
+utils::TCPSocket HostComm::DialTracker() {
+  utils::TCPSocket t;
+  utils::SockAddr addr(cfg.tracker_uri.c_str(), cfg.tracker_port);
+  for (int attempt = 1;; ++attempt) {
+    t.Create();
+    if (t.Connect(addr)) break;
+    t.Close();
+    utils::Check(attempt < std::max(cfg.connect_retry, 1), "cannot reach tracker %s:%d after %d attempts",
+                 cfg.tracker_uri.c_str(), cfg.tracker_port, attempt);
+    fprintf(stderr, "[rabit] tracker %s:%d not reachable, retry %d\n", cfg.tracker_uri.c_str(),
+            cfg.tracker_port, attempt);
+    usleep(200000 * attempt);
+  }
+  int magic = kTrackerMagic;
+  utils::Check(t.SendInt(magic) && t.RecvInt(&magic) && magic == kTrackerMagic,
+               "tracker handshake failed (bad magic)");
+  const int my_rank = rank_assigned_ ? rank : -1;
+  utils::Check(t.SendInt(my_rank) && t.SendInt(world_known_ ? world : cfg.world_size_hint) &&
+               t.SendStr(cfg.task_id), "tracker handshake failed (identity)");
+  return t;
+}
+
+bool HostComm::Connect(const char *cmd) {
+  if (!distributed()) { rank = 0; world = 1; return true; }
+  try {
+    utils::TCPSocket t = this->DialTracker();
+    utils::Check(t.SendStr(cmd), "tracker: cannot send command");
+    int new_rank = -1, nnbr = 0;
+    utils::Check(t.RecvInt(&new_rank) && t.RecvInt(&parent_rank) && t.RecvInt(&world),
+                 "tracker: cannot read assignment");
+    utils::Check(new_rank >= 0, "tracker refused to assign a rank");
+    utils::Assert(!rank_assigned_ || new_rank == rank, "tracker changed our rank from %d to %d", rank, new_rank);
+    rank = new_rank; rank_assigned_ = true; world_known_ = true;
+    std::vector<int> tree_nbrs;
+    utils::Check(t.RecvInt(&nnbr), "tracker: cannot read neighbour count");
+    for (int i = 0; i < nnbr; ++i) {
+      int r; utils::Check(t.RecvInt(&r), "tracker: cannot read neighbour");
+      tree_nbrs.push_back(r);
+    }
+    utils::Check(t.RecvInt(&ring_prev_rank) && t.RecvInt(&ring_next_rank), "tracker: cannot read ring");
+
+    utils::TCPSocket listener;
+    listener.Create();
+    int port;
+    if (cfg.slave_port > 0) {
+      port = listener.TryBindHost(cfg.slave_port, cfg.slave_port + cfg.nport_trial);
+      utils::Check(port != -1, "no free port in [%d, %d)", cfg.slave_port, cfg.slave_port + cfg.nport_trial);
+    } else {
+      port = listener.BindAny();
+    }
+    listener.Listen();
+
+    int nconn = 0, naccept = 0, nerr = 0;
+    do {
+      // report which links survived, drop the rest
+      std::vector<int> good;
+      for (Link &l : links_) {
+        if (l.sock.BadSocket()) l.sock.Close(); else good.push_back(l.rank);
+      }
+      utils::Check(t.SendInt(static_cast<int>(good.size())), "tracker: send failed");
+      for (int r : good) utils::Check(t.SendInt(r), "tracker: send failed");
+      utils::Check(t.RecvInt(&nconn) && t.RecvInt(&naccept), "tracker: cannot read link plan");
+      nerr = 0;
+      for (int i = 0; i < nconn; ++i) {
+        std::string peer_host; int peer_port, peer_rank;
+        utils::Check(t.RecvStr(&peer_host) && t.RecvInt(&peer_port) && t.RecvInt(&peer_rank),
+                     "tracker: cannot read peer address");
+        Link nl;
+        nl.sock.Create();
+        if (!nl.sock.Connect(utils::SockAddr(peer_host.c_str(), peer_port))) {
+          nl.sock.Close(); ++nerr; continue;
+        }
+        int echoed = -1;
+        if (!nl.sock.SendInt(rank) || !nl.sock.RecvInt(&echoed) || echoed != peer_rank) {
+          nl.sock.Close(); ++nerr; continue;
+        }
+        nl.rank = peer_rank;
+        Link *old = FindLink(peer_rank);
+        if (old != nullptr) { old->sock.Close(); old->sock = nl.sock; } else { links_.push_back(nl); }
+      }
+      utils::Check(t.SendInt(nerr), "tracker: send failed");
+    } while (nerr != 0);
+    utils::Check(t.SendInt(port), "tracker: cannot send port");
+    t.Close();
+
+    for (int i = 0; i < naccept; ++i) {
+      Link nl;
+      nl.sock = listener.Accept();
+      utils::Check(nl.sock.SendInt(rank) && nl.sock.RecvInt(&nl.rank), "peer handshake failed");
+      Link *old = FindLink(nl.rank);
+      if (old != nullptr) { old->sock.Close(); old->sock = nl.sock; } else { links_.push_back(nl); }
+    }
+    listener.Close();
+
+    // classify
+    tree_.clear(); parent_slot_ = -1; ring_prev_ = ring_next_ = nullptr;
+    for (Link &l : links_) {
+      utils::Assert(!l.sock.BadSocket(), "link to rank %d is not usable after rendezvous", l.rank);
+      l.sock.SetNonBlock(true);
+      l.sock.SetKeepAlive(true);
+      if (cfg.tcp_no_delay) l.sock.SetNoDelay(true);
+      if (std::find(tree_nbrs.begin(), tree_nbrs.end(), l.rank) != tree_nbrs.end()) {
+        if (l.rank == parent_rank) parent_slot_ = static_cast<int>(tree_.size());
+        tree_.push_back(&l);
+      }
+      if (l.rank == ring_prev_rank) ring_prev_ = &l;
+      if (l.rank == ring_next_rank) ring_next_ = &l;
+    }
+    utils::Assert(parent_rank == -1 || parent_slot_ != -1, "no link to tree parent %d", parent_rank);
+    utils::Assert(ring_prev_rank == -1 || ring_prev_ != nullptr, "no link to ring prev %d", ring_prev_rank);
+    utils::Assert(ring_next_rank == -1 || ring_next_ != nullptr, "no link to ring next %d", ring_next_rank);
+    ++link_generation;
+    return true;
+  } catch (const std::exception &e) {
+    fprintf(stderr, "[rabit] rendezvous (%s) failed: %s\n", cmd, e.what());
+    return false;
+  }
+}
+
+void HostComm::SendShutdown() {
+  if (!distributed() || !rank_assigned_) return;
+  try {
+    utils::TCPSocket t = this->DialTracker();
+    t.SendStr("shutdown");
+    t.Close();
+  } catch (const std::exception &) {
+    // the tracker may already be gone when the job is torn down from outside
+  }
+}
+
+void HostComm::TrackerPrint(const std::string &msg) {
+  if (!distributed()) { utils::Printf("%s", msg.c_str()); fflush(stdout); return; }
+  utils::TCPSocket t = this->DialTracker();
+  t.SendStr("print");
+  t.SendStr(msg);
+  t.Close();
+}
+
+// -------------------------------------------------------------- collectives
+Status HostComm::Allreduce(void *buf, size_t elem_bytes, size_t count, ReduceFunction *reducer) {
+  if (world <= 1 || count == 0) return Status::kOk;
+  if (count > cfg.reduce_ring_mincount) return AllreduceRing(buf, elem_bytes, count, reducer);
+  return AllreduceTree(buf, elem_bytes, count, reducer);
+}
+
+Status HostComm::AllreduceTree(void *buf_, size_t eb, size_t count, ReduceFunction *reducer) {
+  if (tree_.empty() || count == 0) return Status::kOk;
+  char *buf = static_cast<char *>(buf_);
+  const size_t total = eb * count;
+  const bool is_root = parent_slot_ < 0;
+  Link *parent = is_root ? nullptr : tree_[parent_slot_];
+  struct Child { Link *l; size_t recvd; size_t sent_down; char *stage; };
+  std::vector<Child> kids;
+  for (int i = 0; i < static_cast<int>(tree_.size()); ++i) {
+    if (i != parent_slot_) kids.push_back(Child{tree_[i], 0, 0, nullptr});
+  }
+  // per-child staging ring; always a whole number of items so an item never straddles the wrap
+  const size_t cap = FloorTo(std::min(total, cfg.reduce_buffer), eb);
+  if (scratch_.size() < cap * kids.size()) scratch_.resize(cap * kids.size());
+  for (size_t i = 0; i < kids.size(); ++i) kids[i].stage = scratch_.data() + i * cap;
+
+  size_t reduced = kids.empty() ? total : 0;  // prefix of buf that holds the subtree's reduction
+  size_t sent_up = 0, recv_down = 0;
+  const MPI::Datatype dtype(eb);
+  utils::PollHelper poll;
+  while (true) {
+    if (is_root) { sent_up = reduced; recv_down = reduced; }
+    bool done = recv_down == total;
+    for (const Child &c : kids) done = done && c.sent_down == total;
+    if (done) break;
+    poll.Clear();
+    for (const Child &c : kids) {
+      if (c.recvd < total && c.recvd - reduced < cap) poll.WatchRead(c.l->sock.fd);
+      if (c.sent_down < recv_down) poll.WatchWrite(c.l->sock.fd);
+    }
+    if (parent != nullptr) {
+      if (sent_up < reduced) poll.WatchWrite(parent->sock.fd);
+      if (recv_down < sent_up) poll.WatchRead(parent->sock.fd);
+    }
+    poll.Poll();
+    // up: children -> staging
+    for (Child &c : kids) {
+      if (c.recvd < total && c.recvd - reduced < cap && poll.CheckRead(c.l->sock.fd)) {
+        const size_t off = c.recvd % cap;
+        size_t want = std::min(total - c.recvd, cap - (c.recvd - reduced));
+        want = std::min(want, cap - off);
+        size_t got; Status s = RecvSome(c.l, c.stage + off, want, &got);
+        if (!Ok(s)) return s;
+        c.recvd += got;
+      }
+    }
+    // fold whatever every child has delivered
+    if (!kids.empty()) {
+      size_t avail = total;
+      for (const Child &c : kids) avail = std::min(avail, c.recvd);
+      avail = avail / eb * eb;
+      while (reduced < avail) {
+        const size_t off = reduced % cap;
+        const size_t n = std::min(avail - reduced, cap - off);
+        for (Child &c : kids) reducer(c.stage + off, buf + reduced, static_cast<int>(n / eb), dtype);
+        reduced += n;
+      }
+    }
+    if (parent != nullptr) {
+      if (sent_up < reduced && poll.CheckWrite(parent->sock.fd)) {
+        size_t put; Status s = SendSome(parent, buf + sent_up, reduced - sent_up, &put);
+        if (!Ok(s)) return s;
+        sent_up += put;
+      }
+      if (recv_down < sent_up && poll.CheckRead(parent->sock.fd)) {
+        size_t got; Status s = RecvSome(parent, buf + recv_down, sent_up - recv_down, &got);
+        if (!Ok(s)) return s;
+        recv_down += got;
+      }
+    } else {
+      recv_down = reduced;
+    }
+    // down: final values -> children
+    for (Child &c : kids) {
+      if (c.sent_down < recv_down && poll.CheckWrite(c.l->sock.fd)) {
+        size_t put; Status s = SendSome(c.l, buf + c.sent_down, recv_down - c.sent_down, &put);
+        if (!Ok(s)) return s;
+        c.sent_down += put;
+      }
+    }
+  }
+  return Status::kOk;
+}
+
+Status HostComm::Broadcast(void *buf_, size_t size, int root) {
+  if (tree_.empty() || size == 0) return Status::kOk;
+  char *buf = static_cast<char *>(buf_);
+  const int nl = static_cast<int>(tree_.size());
+  // flood over the undirected tree: whoever hands us the first byte is our upstream
+  int upstream = (rank == root) ? -2 : -1;
+  size_t recvd = (rank == root) ? size : 0;
+  std::vector<size_t> sent(nl, 0);
+  utils::PollHelper poll;
+  while (true) {
+    bool done = recvd == size;
+    for (int i = 0; i < nl; ++i) if (i != upstream) done = done && sent[i] == size;
+    if (done) break;
+    poll.Clear();
+    for (int i = 0; i < nl; ++i) {
+      const int fd = tree_[i]->sock.fd;
+      if (upstream == -1 || (i == upstream && recvd < size)) poll.WatchRead(fd);
+      if (upstream != -1 && i != upstream && sent[i] < recvd) poll.WatchWrite(fd);
+    }
+    poll.Poll();
+    if (upstream == -1) {
+      for (int i = 0; i < nl && upstream == -1; ++i) {
+        if (!poll.CheckRead(tree_[i]->sock.fd)) continue;
+        size_t got; Status s = RecvSome(tree_[i], buf, size, &got);
+        if (!Ok(s)) return s;
+        if (got != 0) { upstream = i; recvd = got; }
+      }
+      continue;  // re-arm the poll set now that directions are known
+    }
+    if (upstream >= 0 && recvd < size && poll.CheckRead(tree_[upstream]->sock.fd)) {
+      size_t got; Status s = RecvSome(tree_[upstream], buf + recvd, size - recvd, &got);
+      if (!Ok(s)) return s;
+      recvd += got;
+    }
+    for (int i = 0; i < nl; ++i) {
+      if (i == upstream || sent[i] >= recvd || !poll.CheckWrite(tree_[i]->sock.fd)) continue;
+      size_t put; Status s = SendSome(tree_[i], buf + sent[i], recvd - sent[i], &put);
+      if (!Ok(s)) return s;
+      sent[i] += put;
+    }
+  }
+  return Status::kOk;
+}
+
+Status HostComm::AllgatherRing(void *buf_, size_t total, size_t slice_begin, size_t slice_end,
+                               size_t size_prev_slice) {
+  if (ring_prev_ == nullptr || ring_next_ == nullptr || total == 0) return Status::kOk;
+  utils::Assert(slice_begin <= slice_end && slice_end <= total, "Allgather: slice [%lu,%lu) outside %lu",
+                (unsigned long)slice_begin, (unsigned long)slice_end, (unsigned long)total);  // NOLINT(*)
+  char *buf = static_cast<char *>(buf_);
+  // Bytes stream "downwards" in rank: in from the successor, out to the predecessor. Seen
+  // as a ring of `total` bytes both streams are contiguous and ascending: what arrives
+  // continues right after our slice, what leaves starts at our slice.
+  const size_t mine = slice_end - slice_begin;
+  const size_t total_recv = total - mine;
+  const size_t total_send = total - size_prev_slice;
+  size_t recvd = 0, sent = 0;
+  utils::PollHelper poll;
+  while (recvd < total_recv || sent < total_send) {
+    const size_t sendable = std::min(total_send, mine + recvd);
+    poll.Clear();
+    if (recvd < total_recv) poll.WatchRead(ring_next_->sock.fd);
+    if (sent < sendable) poll.WatchWrite(ring_prev_->sock.fd);
+    poll.Poll();
+    if (recvd < total_recv && poll.CheckRead(ring_next_->sock.fd)) {
+      const size_t pos = (slice_end + recvd) % total;
+      size_t got; Status s = RecvSome(ring_next_, buf + pos, std::min(total_recv - recvd, total - pos), &got);
+      if (!Ok(s)) return s;
+      recvd += got;
+    }
+    if (sent < sendable && poll.CheckWrite(ring_prev_->sock.fd)) {
+      const size_t pos = (slice_begin + sent) % total;
+      size_t put; Status s = SendSome(ring_prev_, buf + pos, std::min(sendable - sent, total - pos), &put);
+      if (!Ok(s)) return s;
+      sent += put;
+    }
+  }
+  return Status::kOk;
+}
+
+Status HostComm::ReduceScatterRing(void *buf_, size_t eb, size_t count, ReduceFunction *reducer) {
+  if (ring_prev_ == nullptr || ring_next_ == nullptr || count == 0) return Status::kOk;
+  char *buf = static_cast<char *>(buf_);
+  const size_t n = static_cast<size_t>(world);
+  const size_t step = (count + n - 1) / n;
+  const size_t total = count * eb;
+  auto seg_begin = [&](size_t j) { return std::min((j % n) * step, count) * eb; };
+  auto seg_len = [&](size_t j) { return std::min((j % n + 1) * step, count) * eb - seg_begin(j); };
+  // Partial sums travel towards lower ranks. We emit segments r+1, r+2, ..., r+n-1 and absorb
+  // r+2, ..., r+n (= r, the one we end up owning); as byte ranges of the ring both are contiguous.
+  const size_t r = static_cast<size_t>(rank);
+  const size_t send_start = seg_begin(r + 1);
+  const size_t recv_start = seg_begin(r + 2);
+  const size_t total_send = total - seg_len(r);
+  const size_t total_recv = total - seg_len(r + 1);
+  const size_t head = seg_len(r + 1);  // our own data: can leave before anything is folded
+  const size_t cap = FloorTo(std::min(total, cfg.reduce_buffer), eb);
+  if (scratch_.size() < cap) scratch_.resize(cap);
+  char *stage = scratch_.data();
+  size_t recvd = 0, reduced = 0, sent = 0;
+  const MPI::Datatype dtype(eb);
+  utils::PollHelper poll;
+  while (sent < total_send || reduced < total_recv) {
+    size_t sendable = std::min(total_send, head + reduced);
+    poll.Clear();
+    const bool can_read = recvd < total_recv && recvd - reduced < cap;
+    if (can_read) poll.WatchRead(ring_next_->sock.fd);
+    if (sent < sendable) poll.WatchWrite(ring_prev_->sock.fd);
+    poll.Poll();
+    if (can_read && poll.CheckRead(ring_next_->sock.fd)) {
+      const size_t off = recvd % cap;
+      size_t want = std::min(total_recv - recvd, cap - (recvd - reduced));
+      want = std::min(want, cap - off);
+      size_t got; Status s = RecvSome(ring_next_, stage + off, want, &got);
+      if (!Ok(s)) return s;
+      recvd += got;
+    }
+    const size_t avail = recvd / eb * eb;
+    while (reduced < avail) {
+      const size_t off = reduced % cap;
+      const size_t pos = (recv_start + reduced) % total;
+      size_t len = std::min(avail - reduced, cap - off);
+      len = std::min(len, total - pos);
+      reducer(stage + off, buf + pos, static_cast<int>(len / eb), dtype);
+      reduced += len;
+    }
+    sendable = std::min(total_send, head + reduced);
+    if (sent < sendable && poll.CheckWrite(ring_prev_->sock.fd)) {
+      const size_t pos = (send_start + sent) % total;
+      size_t put; Status s = SendSome(ring_prev_, buf + pos, std::min(sendable - sent, total - pos), &put);
+      if (!Ok(s)) return s;
+      sent += put;
+    }
+  }
+  return Status::kOk;
+}
+
+Status HostComm::AllreduceRing(void *buf, size_t eb, size_t count, ReduceFunction *reducer) {
+  Status s = ReduceScatterRing(buf, eb, count, reducer);
+  if (!Ok(s)) return s;
+  const size_t n = static_cast<size_t>(world);
+  const size_t step = (count + n - 1) / n;
+  auto seg_begin = [&](size_t j) { return std::min(j * step, count); };
+  const size_t r = static_cast<size_t>(rank), p = (r + n - 1) % n;
+  return AllgatherRing(buf, count * eb, seg_begin(r) * eb, seg_begin(r + 1) * eb,
+                       (seg_begin(p + 1) - seg_begin(p)) * eb);
+}
+
+// --------------------------------------------------------------- ring movers
+Status HostComm::RelayImpl(Link *from, Link *to, void *buf_, size_t size) {
+  char *buf = static_cast<char *>(buf_);
+  size_t recvd = from != nullptr ? 0 : size;
+  size_t sent = to != nullptr ? 0 : size;
+  utils::PollHelper poll;
+  while (recvd < size || sent < size) {
+    poll.Clear();
+    if (recvd < size) poll.WatchRead(from->sock.fd);
+    if (sent < recvd) poll.WatchWrite(to->sock.fd);
+    poll.Poll();
+    if (recvd < size && poll.CheckRead(from->sock.fd)) {
+      size_t got; Status s = RecvSome(from, buf + recvd, size - recvd, &got);
+      if (!Ok(s)) return s;
+      recvd += got;
+    }
+    if (sent < recvd && poll.CheckWrite(to->sock.fd)) {
+      size_t put; Status s = SendSome(to, buf + sent, recvd - sent, &put);
+      if (!Ok(s)) return s;
+      sent += put;
+    }
+  }
+  return Status::kOk;
+}
+
+Status HostComm::RingRelay(void *buf, size_t size, bool recv_from_prev, bool send_to_next) {
+  if (size == 0 || (!recv_from_prev && !send_to_next)) return Status::kOk;
+  utils::Assert(ring_prev_ != nullptr && ring_next_ != nullptr, "RingRelay without a ring");
+  return RelayImpl(recv_from_prev ? ring_prev_ : nullptr, send_to_next ? ring_next_ : nullptr, buf, size);
+}
+
+Status HostComm::RingRelayBack(void *buf, size_t size, bool recv_from_next, bool send_to_prev) {
+  if (size == 0 || (!recv_from_next && !send_to_prev)) return Status::kOk;
+  utils::Assert(ring_prev_ != nullptr && ring_next_ != nullptr, "RingRelayBack without a ring");
+  return RelayImpl(recv_from_next ? ring_next_ : nullptr, send_to_prev ? ring_prev_ : nullptr, buf, size);
+}
+
+Status HostComm::RingShift(const void *send_, size_t nsend, void *recv_, size_t nrecv, bool forward) {
+  if (nsend == 0 && nrecv == 0) return Status::kOk;
+  utils::Assert(ring_prev_ != nullptr && ring_next_ != nullptr, "RingShift without a ring");
+  Link *to = forward ? ring_next_ : ring_prev_;
+  Link *from = forward ? ring_prev_ : ring_next_;
+  const char *send = static_cast<const char *>(send_);
+  char *recv = static_cast<char *>(recv_);
+  size_t sent = 0, recvd = 0;
+  utils::PollHelper poll;
+  while (sent < nsend || recvd < nrecv) {
+    poll.Clear();
+    if (recvd < nrecv) poll.WatchRead(from->sock.fd);
+    if (sent < nsend) poll.WatchWrite(to->sock.fd);
+    poll.Poll();
+    if (recvd < nrecv && poll.CheckRead(from->sock.fd)) {
+      size_t got; Status s = RecvSome(from, recv + recvd, nrecv - recvd, &got);
+      if (!Ok(s)) return s;
+      recvd += got;
+    }
+    if (sent < nsend && poll.CheckWrite(to->sock.fd)) {
+      size_t put; Status s = SendSome(to, send + sent, nsend - sent, &put);
+      if (!Ok(s)) return s;
+      sent += put;
+    }
+  }
+  return Status::kOk;
+}
+
+}  // namespace engine
+}  // namespace rabit

@@ -1,0 +1,116 @@
+/*!
+ * rabit-b200: host-memory transport — tracker client, peer links and the fallible
+ * collective primitives everything else is built from.
+ *
+ * Role parity with reference src/allreduce_base.{h,cc} (tracker handshake 221-438, tree
+ * allreduce 476-668, flood broadcast 677-765, ring allgather 779-843, ring reduce-scatter
+ * 857-946). The structure is different on purpose: every primitive is a small byte-flow
+ * state machine driven by one shared poll loop (`Pump`), and recovery payloads move with
+ * `RingRelay` along the rank ring instead of being routed over the tree.
+ *
+ * Every Try-style call returns a Status instead of throwing: a lost peer is a normal
+ * event that the robust engine turns into "close everything, re-rendezvous, re-decide".
+ */
+#ifndef RABIT_SRC_HOST_COMM_H_
+#define RABIT_SRC_HOST_COMM_H_
+
+#include <string>
+#include <vector>
+
+#include "config.h"
+#include "rabit/internal/engine.h"
+#include "rabit/internal/socket.h"
+
+namespace rabit {
+namespace engine {
+
+/*! \brief outcome of a fallible primitive */
+enum class Status {
+  kOk = 0,
+  kPeerClosed,   // orderly close or reset by peer: the peer died or is itself recovering
+  kSockError,    // any other socket level failure
+  kTimeout,      // device backend only: a peer did not show up in the bounded spin
+  kMismatch      // device backend only: fused consensus saw different requests
+};
+inline bool Ok(Status s) { return s == Status::kOk; }
+const char *StatusName(Status s);
+
+/*! \brief one established peer connection */
+struct Link {
+  utils::TCPSocket sock;
+  int rank = -1;
+};
+
+class HostComm {
+ public:
+  typedef IEngine::ReduceFunction ReduceFunction;
+
+  HostComm();
+  ~HostComm();
+
+  // ---- identity ----
+  Config cfg;
+  int rank = 0;
+  int world = 1;
+  int parent_rank = -1;
+  int ring_prev_rank = -1;
+  int ring_next_rank = -1;
+  std::string host;
+  /*! \brief bumped on every successful (re)connect; device backend keys its mappings on it */
+  int link_generation = 0;
+
+  bool distributed() const { return cfg.tracker_uri != "NULL"; }
+
+  // ---- rendezvous ----
+  /*! \brief talk to the tracker with cmd "start" or "recover" and (re)build every link */
+  bool Connect(const char *cmd);
+  /*! \brief drop every peer connection (peers see it as our failure and follow suit) */
+  void CloseLinks();
+  /*! \brief tell the tracker this rank is done */
+  void SendShutdown();
+  /*! \brief log line on the tracker, or stdout without one */
+  void TrackerPrint(const std::string &msg);
+
+  // ---- collectives on host memory ----
+  Status Allreduce(void *buf, size_t elem_bytes, size_t count, ReduceFunction *reducer);
+  Status AllreduceTree(void *buf, size_t elem_bytes, size_t count, ReduceFunction *reducer);
+  Status AllreduceRing(void *buf, size_t elem_bytes, size_t count, ReduceFunction *reducer);
+  Status ReduceScatterRing(void *buf, size_t elem_bytes, size_t count, ReduceFunction *reducer);
+  Status AllgatherRing(void *buf, size_t total, size_t slice_begin, size_t slice_end,
+                       size_t size_prev_slice);
+  Status Broadcast(void *buf, size_t size, int root);
+
+  // ---- ring movers used by checkpoint replication and recovery ----
+  /*!
+   * \brief pipelined pass-along: optionally receive `size` bytes from the ring predecessor
+   *  into buf and optionally forward buf to the ring successor (forwarding never runs
+   *  ahead of what has been received).
+   */
+  Status RingRelay(void *buf, size_t size, bool recv_from_prev, bool send_to_next);
+  /*! \brief the same in the opposite direction (from successor, to predecessor) */
+  Status RingRelayBack(void *buf, size_t size, bool recv_from_next, bool send_to_prev);
+  /*!
+   * \brief independent send and receive with the two ring neighbours. forward: send to the
+   *  successor / receive from the predecessor; otherwise the other way round. Either size
+   *  may be zero.
+   */
+  Status RingShift(const void *send, size_t nsend, void *recv, size_t nrecv, bool forward);
+
+ private:
+  utils::TCPSocket DialTracker();
+  Link *FindLink(int r);
+  Status RelayImpl(Link *from, Link *to, void *buf, size_t size);
+
+  std::vector<Link> links_;          // every live peer connection
+  std::vector<Link *> tree_;         // subset: tree neighbours
+  int parent_slot_ = -1;             // index into tree_ of the parent, -1 on the root
+  Link *ring_prev_ = nullptr;
+  Link *ring_next_ = nullptr;
+  std::vector<char> scratch_;        // staging for reductions
+  bool rank_assigned_ = false;       // the tracker has told us who we are
+  bool world_known_ = false;
+};
+
+}  // namespace engine
+}  // namespace rabit
+#endif  // RABIT_SRC_HOST_COMM_H_

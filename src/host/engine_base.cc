@@ -1,0 +1,127 @@
+/*!
+ * rabit-b200: BaseEngine — collectives without fault tolerance. Any transport failure is
+ * fatal here (reference AllreduceBase used as an engine: allreduce_base.h:104-160).
+ */
+#include <unistd.h>
+
+#include "../device/device_backend.h"
+#include "engine_core.h"
+
+namespace rabit {
+namespace engine {
+
+BaseEngine::BaseEngine() {}
+BaseEngine::~BaseEngine() {}
+
+MemKind BaseEngine::Classify(const void *ptr) const {
+  if (ptr == nullptr) return MemKind::kHost;
+  return DeviceBackend::IsDevicePointer(ptr) ? MemKind::kDevice : MemKind::kHost;
+}
+
+bool BaseEngine::Init(int argc, char *argv[]) {
+  comm_.cfg.Load(argc, argv);
+  // Hadoop streaming sniffing (reference allreduce_base.cc:66-100): task ids and world size
+  // come from the job environment when rabit runs inside a mapper.
+  if (comm_.cfg.task_id == "NULL") {
+    const char *tip = getenv("mapred_tip_id");
+    if (tip == nullptr) tip = getenv("mapreduce_task_id");
+    if (tip != nullptr) { comm_.cfg.task_id = tip; comm_.cfg.hadoop_mode = 1; }
+  }
+  if (comm_.cfg.hadoop_mode != 0) {
+    const char *att = getenv("mapred_task_id");
+    if (att == nullptr) att = getenv("mapreduce_task_attempt_id");
+    if (att != nullptr) {
+      const char *us = strrchr(att, '_');
+      int n;
+      if (us != nullptr && sscanf(us + 1, "%d", &n) == 1) comm_.cfg.num_trial = n;
+    }
+    const char *nmap = getenv("mapred_map_tasks");
+    if (nmap == nullptr) nmap = getenv("mapreduce_job_maps");
+    if (nmap != nullptr) comm_.cfg.world_size_hint = atoi(nmap);
+  }
+  if (comm_.cfg.role != "worker") {
+    // servers / schedulers of a dmlc job have nothing to do in an allreduce program
+    fprintf(stderr, "Rabit Module currently only work with dmlc worker, quit this program by exit 0\n");
+    exit(0);
+  }
+  comm_.host = utils::SockAddr::GetHostName();
+  if (!comm_.Connect("start")) return false;
+  if (comm_.world > 1 || comm_.cfg.device_force) {
+    device_.reset(DeviceBackend::Create(comm_.cfg));
+    if (device_ && !device_->Attach(&comm_)) {
+      utils::Check(comm_.cfg.device != "on", "rabit_device=on but the device arena could not be set up");
+      device_.reset();
+    }
+  }
+  initialized_ = true;
+  return true;
+}
+
+bool BaseEngine::Shutdown(void) {
+  if (device_) { device_->Detach(); device_.reset(); }
+  comm_.CloseLinks();
+  comm_.SendShutdown();
+  initialized_ = false;
+  return true;
+}
+
+namespace {
+void Fatal(Status s, const char *what) {
+  utils::Error("%s failed: %s (the base engine cannot recover; use the robust engine)", what, StatusName(s));
+}
+}  // namespace
+
+void BaseEngine::AllreduceTyped(void *buf, size_t type_nbytes, size_t count, ReduceFunction reducer,
+                                int dtype, int op, PreprocFunction prepare_fun, void *prepare_arg,
+                                const char *, const int, const char *) {
+  if (prepare_fun != nullptr) prepare_fun(prepare_arg);
+  if (comm_.world <= 1 && !(device_ && comm_.cfg.device_force)) return;
+  if (Classify(buf) == MemKind::kDevice) {
+    utils::Check(device_ != nullptr, "Allreduce on a device pointer but the device backend is not available");
+    if (dtype >= 0 && op >= 0) {
+      Status s = device_->Allreduce(buf, count, dtype, op, 1, 0, nullptr);
+      if (!Ok(s)) Fatal(s, "device allreduce");
+      return;
+    }
+    // opaque reducer: stage through the host
+    std::string tmp(type_nbytes * count, '\0');
+    device_->CopyD2H(&tmp[0], buf, tmp.size());
+    Status s = comm_.Allreduce(&tmp[0], type_nbytes, count, reducer);
+    if (!Ok(s)) Fatal(s, "allreduce");
+    device_->CopyH2D(buf, tmp.data(), tmp.size());
+    return;
+  }
+  Status s = comm_.Allreduce(buf, type_nbytes, count, reducer);
+  if (!Ok(s)) Fatal(s, "allreduce");
+  ++seq_;
+}
+
+void BaseEngine::Broadcast(void *buf, size_t size, int root, const char *, const int, const char *) {
+  if (comm_.world <= 1) return;
+  if (Classify(buf) == MemKind::kDevice) {
+    utils::Check(device_ != nullptr, "Broadcast on a device pointer but the device backend is not available");
+    Status s = device_->Broadcast(buf, size, root, 0, nullptr);
+    if (!Ok(s)) Fatal(s, "device broadcast");
+    return;
+  }
+  Status s = comm_.Broadcast(buf, size, root);
+  if (!Ok(s)) Fatal(s, "broadcast");
+  ++seq_;
+}
+
+void BaseEngine::Allgather(void *buf, size_t total_size, size_t slice_begin, size_t slice_end,
+                           size_t size_prev_slice, const char *, const int, const char *) {
+  if (comm_.world <= 1) return;
+  if (Classify(buf) == MemKind::kDevice) {
+    utils::Check(device_ != nullptr, "Allgather on a device pointer but the device backend is not available");
+    Status s = device_->Allgather(buf, total_size, slice_begin, slice_end, 0, nullptr);
+    if (!Ok(s)) Fatal(s, "device allgather");
+    return;
+  }
+  Status s = comm_.AllgatherRing(buf, total_size, slice_begin, slice_end, size_prev_slice);
+  if (!Ok(s)) Fatal(s, "allgather");
+  ++seq_;
+}
+
+}  // namespace engine
+}  // namespace rabit

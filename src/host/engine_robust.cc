@@ -1,0 +1,189 @@
+/*!
+ * rabit-b200: RobustEngine — sequence-numbered result cache, consensus-driven recovery,
+ * two-phase in-memory checkpoints, ring-replicated local models, bootstrap cache, watchdog.
+ *
+ * Semantics follow reference src/allreduce_robust.cc (collective wrappers 172-360,
+ * LoadCheckPoint 383-446, CheckPoint_ 484-557, CheckAndRecover 687-725, RecoverExec
+ * 1158-1311, local-state ring recovery 1328-1587); the mechanism is this build's own:
+ *   - consensus = proto::Decide over an allreduced Summary (protocol.h);
+ *   - holders/requesters are discovered with GatherTable, so ANY rank that still has the
+ *     bytes can serve, and every rank computes the same transfer plan locally;
+ *   - payloads travel along the rank ring (RingDeliver) — on an NVSwitch box "routing" is
+ *     meaningless, and on TCP the ring links already exist.
+ */
+#include <chrono>
+#include <thread>
+
+#include "../device/device_backend.h"
+#include "engine_core.h"
+
+namespace rabit {
+namespace engine {
+
+using proto::Request;
+using proto::Summary;
+
+RobustEngine::RobustEngine() {}
+
+RobustEngine::~RobustEngine() {
+  watchdog_cancel_ = true;
+  if (watchdog_.joinable()) watchdog_.join();
+}
+
+bool RobustEngine::Init(int argc, char *argv[]) {
+  if (!BaseEngine::Init(argc, argv)) return false;
+  if (comm_.cfg.bootstrap_cache) utils::HandleLogInfo("[rabit] bootstrap cache enabled\n");
+  num_local_replica_ = comm_.cfg.local_replica;
+  checkpoint_loaded_ = false;
+  results_.SetDevice(device_.get());
+  return true;
+}
+
+int RobustEngine::ReplicaRound() const {
+  // a result with sequence number s is retained on ranks r with r % round == s % round, i.e.
+  // on about `global_replica` ranks (reference allreduce_robust.cc:47-51); -1 = keep nothing old
+  if (comm_.cfg.global_replica == 0) return -1;
+  return std::max(comm_.world / comm_.cfg.global_replica, 1);
+}
+
+bool RobustEngine::Shutdown(void) {
+  try {
+    if (comm_.world > 1) {
+      // Leave through a pseudo commit so nobody exits while a peer still needs its cache.
+      utils::Assert(Consensus(nullptr, 0, proto::kCheckPoint, proto::kSeqSpecial), "shutdown barrier 1");
+      results_.Clear(); seq_ = 0; boot_cache_.clear();
+      utils::Assert(Consensus(nullptr, 0, proto::kCheckAck, proto::kSeqSpecial), "shutdown barrier 2");
+    }
+    StopWatchdog();
+    results_.Clear();
+    results_.SetDevice(nullptr);
+    return BaseEngine::Shutdown();
+  } catch (const std::exception &e) {
+    fprintf(stderr, "[rabit] shutdown: %s\n", e.what());
+    return false;
+  }
+}
+
+void RobustEngine::InitAfterException(void) {
+  // the caller swallowed an engine exception and wants to carry on in this process
+  if (device_) device_->Detach();
+  comm_.CloseLinks();
+  while (!comm_.Connect("recover")) std::this_thread::sleep_for(std::chrono::milliseconds(100));
+  if (device_) device_->Attach(&comm_);
+}
+
+// ------------------------------------------------------------------ failures
+void RobustEngine::StartWatchdog() {
+  if (!comm_.cfg.timeout_enabled || watchdog_.joinable()) return;
+  utils::Printf("[rabit] recovery watchdog armed: %d s\n", comm_.cfg.timeout_sec);
+  watchdog_cancel_ = false; watchdog_done_ = false; watchdog_fired_ = false;
+  const int secs = comm_.cfg.timeout_sec, me = comm_.rank;
+  void (*hook)(int, int) = on_timeout;
+  watchdog_ = std::thread([this, secs, me, hook]() {
+    for (int tick = 0; tick < secs * 10; ++tick) {
+      std::this_thread::sleep_for(std::chrono::milliseconds(100));
+      if (watchdog_cancel_.load()) { watchdog_done_ = true; return; }
+    }
+    watchdog_fired_ = true; watchdog_done_ = true;
+    fprintf(stderr, "[%d] exit due to time out %d s\n", me, secs);
+    fflush(stderr);
+    if (hook != nullptr) { hook(me, secs); return; }
+    // The reference only throws inside the async task, which nobody observes;
+    // the documented intent is to stop the worker, so do that.
+    _exit(10);
+  });
+}
+
+void RobustEngine::StopWatchdog() {
+  if (!watchdog_.joinable()) return;
+  watchdog_cancel_ = true;
+  watchdog_.join();
+}
+
+bool RobustEngine::Healthy(Status s) {
+  if (Ok(s)) { StopWatchdog(); return true; }
+  ++recover_counter_;
+  if (comm_.cfg.debug) {
+    utils::HandleLogInfo("[%d] link failure (%s) at version %d seq %d, re-joining\n", comm_.rank,
+                         StatusName(s), version_number_, seq_);
+  }
+  StartWatchdog();
+  // Drop EVERY link: neighbours observe it as a failure too and the whole job funnels into the
+  // tracker's "recover" rendezvous, where it waits for the replacement process.
+  if (device_) device_->Detach();
+  comm_.CloseLinks();
+  std::this_thread::sleep_for(std::chrono::milliseconds(2 * comm_.rank));
+  while (!comm_.Connect("recover")) std::this_thread::sleep_for(std::chrono::milliseconds(100));
+  if (device_ && !device_->Attach(&comm_)) {
+    utils::Error("[%d] device arena could not be re-established after recovery", comm_.rank);
+  }
+  return false;
+}
+
+// ----------------------------------------------------------------- consensus
+bool RobustEngine::Consensus(void *buf, size_t size, uint32_t flags, uint32_t seq) {
+  Request me{seq, flags, static_cast<uint32_t>(boot_cache_.size())};
+  while (true) {
+    this->ReportStatus();
+    me.cache_count = static_cast<uint32_t>(boot_cache_.size());
+    Summary sum = Summary::Of(me);
+    if (!Healthy(comm_.Allreduce(&sum, sizeof(sum), 1, proto::SummaryReduce))) continue;
+    const proto::Verdict v = proto::Decide(sum, me);
+    switch (v.action) {
+      case proto::kExecute: return false;
+      case proto::kDone: return true;
+      case proto::kRetry: break;
+      case proto::kServeLoad:
+        if (Healthy(ServeLoad(v.requester)) && v.requester) return true;
+        break;
+      case proto::kServeCache:
+        if (comm_.cfg.debug) {
+          utils::HandleLogInfo("[%d] bootstrap cache sync: mine %u, max %u, requester %d\n", comm_.rank,
+                               me.cache_count, sum.max_cache, static_cast<int>(v.requester));
+        }
+        utils::Check(!((flags & proto::kLoadCache) && !v.requester && !sum.all(proto::kLoadCache)),
+                     "[%d] bootstrap collective is not in the peers' cache: the calling sequence before "
+                     "LoadCheckPoint differs between runs", comm_.rank);
+        if (Healthy(ServeCache(v.requester, sum.max_cache)) && v.requester) return true;
+        break;
+      case proto::kServeResult:
+        if (Healthy(ServeResult(buf, size, sum.min_seq, v.requester)) && v.requester) return true;
+        break;
+    }
+  }
+}
+
+Status RobustEngine::GatherTable(const uint64_t *mine, int nwords, std::vector<uint64_t> *table) {
+  table->assign(static_cast<size_t>(comm_.world) * nwords, 0);
+  for (int i = 0; i < nwords; ++i) (*table)[static_cast<size_t>(comm_.rank) * nwords + i] = mine[i];
+  // everyone contributes zeros outside its own row, so a bitwise OR assembles the table
+  return comm_.AllreduceTree(table->data(), sizeof(uint64_t), table->size(),
+                             [](const void *s, void *d, int n, const MPI::Datatype &) {
+                               const uint64_t *src = static_cast<const uint64_t *>(s);
+                               uint64_t *dst = static_cast<uint64_t *>(d);
+                               for (int i = 0; i < n; ++i) dst[i] |= src[i];
+                             });
+}
+
+Status RobustEngine::RingDeliver(const std::vector<char> &has, const std::vector<char> &need,
+                                 void *buf, size_t size) {
+  // Bytes flow forward (r -> r+1). A rank without the bytes must take them from its predecessor
+  // if some requester sits between it (inclusive) and the next holder downstream.
+  const int n = comm_.world, me = comm_.rank;
+  auto must_recv = [&](int r) {
+    if (has[r]) return false;
+    for (int q = r, hops = 0; hops < n && !has[q]; q = (q + 1) % n, ++hops) {
+      if (need[q]) return true;
+    }
+    return false;
+  };
+  const bool recv = must_recv(me);
+  const bool send = must_recv((me + 1) % n);
+  if (!recv && !send) return Status::kOk;
+  std::string pass;  // pure relays need a landing zone
+  if (buf == nullptr) { pass.resize(size); buf = &pass[0]; }
+  return comm_.RingRelay(buf, size, recv, send);
+}
+
+}  // namespace engine
+}  // namespace rabit
