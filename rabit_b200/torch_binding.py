@@ -1,0 +1,146 @@
+"""PyTorch binding: rabit collectives on ``torch`` tensors.
+
+CUDA tensors are handed to the engine by address; the engine recognises device pointers
+and runs the fused sm_100a kernels on them (robust path: consensus fused into the kernel,
+result cached on the GPU).  CPU tensors go through their numpy view to the host engine.
+``*_async`` variants only enqueue on the current CUDA stream (no fault tolerance, no host
+synchronisation) and are what training loops and CUDA-graph capture want.
+
+No counterpart in the reference (it predates GPU tensors); the semantics of each call are
+those of ``rabit::Allreduce/Broadcast/Allgather`` (reference include/rabit/rabit.h).
+"""
+import ctypes
+
+import torch
+
+from . import rabit as _rabit
+
+_TORCH_DTYPE = {
+    torch.int8: 0, torch.uint8: 1, torch.int32: 2, torch.int64: 4,
+    torch.float32: 6, torch.float64: 7,
+}
+_ITEMSIZE = {0: 1, 1: 1, 2: 4, 3: 4, 4: 8, 5: 8, 6: 4, 7: 8}
+
+
+def _lib():
+    lib = _rabit.get_lib()
+    if lib is None:
+        raise RuntimeError("call rabit_b200.rabit.init() first")
+    if not getattr(lib, "_rabit_device_declared", False):
+        c = ctypes
+        lib.RabitDeviceAllreduceAsync.argtypes = [c.c_void_p, c.c_size_t, c.c_int, c.c_int]
+        lib.RabitDeviceBroadcastAsync.argtypes = [c.c_void_p, c.c_size_t, c.c_int]
+        lib.RabitDeviceAllgatherAsync.argtypes = [c.c_void_p, c.c_size_t, c.c_size_t, c.c_size_t]
+        lib.RabitDeviceSetStream.argtypes = [c.c_void_p]
+        lib.RabitDeviceLaunchCount.restype = c.c_ulonglong
+        lib.RabitDeviceDescribe.argtypes = [c.c_char_p, c.c_size_t]
+        lib._rabit_device_declared = True
+    return lib
+
+
+def _dtype_enum(t):
+    if t.dtype not in _TORCH_DTYPE:
+        raise TypeError("dtype %s is not supported by rabit allreduce" % t.dtype)
+    return _TORCH_DTYPE[t.dtype]
+
+
+def _check(t):
+    if not t.is_contiguous():
+        raise ValueError("rabit collectives need contiguous tensors")
+
+
+def _bind_stream(lib, t):
+    if t.is_cuda:
+        lib.RabitDeviceSetStream(ctypes.c_void_p(torch.cuda.current_stream(t.device).cuda_stream))
+
+
+def describe():
+    """One line about the device backend (arena kind, NVLS on/off ...)."""
+    lib = _lib()
+    buf = ctypes.create_string_buffer(1024)
+    lib.RabitDeviceDescribe(buf, 1024)
+    return buf.value.decode()
+
+
+def device_active():
+    return bool(_lib().RabitDeviceActive())
+
+
+def launch_count():
+    """Number of this library's kernels launched so far in this process."""
+    return int(_lib().RabitDeviceLaunchCount())
+
+
+def allreduce_(tensor, op=_rabit.SUM, prepare_fun=None):
+    """Fault-tolerant in-place allreduce; returns ``tensor``.  Blocks until the result is in
+    ``tensor`` on this rank (rabit semantics)."""
+    lib = _lib()
+    _check(tensor)
+    keep = None
+    fptr = None
+    if prepare_fun is not None:
+        proto = ctypes.CFUNCTYPE(None, ctypes.c_void_p)
+
+        def pfunc(_):
+            prepare_fun(tensor)
+            if tensor.is_cuda:
+                torch.cuda.current_stream(tensor.device).synchronize()
+        keep = proto(pfunc)
+        fptr = ctypes.cast(keep, ctypes.c_void_p)
+    if tensor.is_cuda:
+        _bind_stream(lib, tensor)
+    lib.RabitAllreduce(ctypes.c_void_p(tensor.data_ptr()), tensor.numel(), _dtype_enum(tensor), op, fptr, None)
+    return tensor
+
+
+def broadcast_(tensor, root=0):
+    """Fault-tolerant in-place broadcast of the tensor's bytes from ``root``."""
+    lib = _lib()
+    _check(tensor)
+    if tensor.is_cuda:
+        _bind_stream(lib, tensor)
+    lib.RabitBroadcast(ctypes.c_void_p(tensor.data_ptr()), tensor.numel() * tensor.element_size(), root)
+    return tensor
+
+
+def allgather_(out, begin, count, prev_count=None):
+    """Fault-tolerant ring-ordered allgather: this rank owns ``out.view(-1)[begin:begin+count]``."""
+    lib = _lib()
+    _check(out)
+    if out.is_cuda:
+        _bind_stream(lib, out)
+    if prev_count is None:
+        prev_count = count
+    lib.RabitAllgather(ctypes.c_void_p(out.data_ptr()), out.numel(), begin, count, prev_count, _dtype_enum(out))
+    return out
+
+
+def allreduce_async_(tensor, op=_rabit.SUM):
+    """Enqueue an in-place allreduce on the current CUDA stream and return immediately."""
+    lib = _lib()
+    _check(tensor)
+    if not tensor.is_cuda:
+        raise ValueError("allreduce_async_ needs a CUDA tensor")
+    _bind_stream(lib, tensor)
+    rc = lib.RabitDeviceAllreduceAsync(ctypes.c_void_p(tensor.data_ptr()), tensor.numel(), _dtype_enum(tensor), op)
+    if rc != 0:
+        raise RuntimeError("RabitDeviceAllreduceAsync failed (%d)" % rc)
+    return tensor
+
+
+def broadcast_async_(tensor, root=0):
+    lib = _lib()
+    _check(tensor)
+    _bind_stream(lib, tensor)
+    rc = lib.RabitDeviceBroadcastAsync(ctypes.c_void_p(tensor.data_ptr()), tensor.numel() * tensor.element_size(), root)
+    if rc != 0:
+        raise RuntimeError("RabitDeviceBroadcastAsync failed (%d)" % rc)
+    return tensor
+
+
+def synchronize():
+    """Wait for the enqueued collectives; raises if a peer was lost or timed out."""
+    rc = _lib().RabitDeviceSynchronize()
+    if rc != 0:
+        raise RuntimeError("device collective failed: %s" %
+                           {1: "consensus mismatch", 2: "peer timeout", 3: "peer lost"}.get(rc, rc))

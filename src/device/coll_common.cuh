@@ -1,0 +1,224 @@
+/*!
+ * rabit-b200: device-side building blocks of the peer-memory collectives (sm_100a).
+ *
+ * No counterpart in the reference (CPU/TCP only). What its AllreduceBase does with a
+ * binary tree and a ring of sockets (src/allreduce_base.cc:476-977) is done here by
+ * kernels that load/store the other GPUs' memory directly over NVLink 5 / NVSwitch:
+ *
+ *   symmetric arena   every rank maps every rank's arena; same layout everywhere:
+ *                     [control block | stage 0 | stage 1]
+ *   channels          block b of every rank works on the same tile set and only ever
+ *                     synchronises with block b of the peers (per-block flag rows), so
+ *                     there is no grid-wide barrier and blocks drift freely
+ *   flag barrier      monotonically increasing 64-bit words written with st.release.sys
+ *                     into the PEER's control block, polled locally with ld.acquire.sys
+ *   fused consensus   the low 32 bits of the entry-barrier flag carry the rank's
+ *                     protocol code (proto::Request::Code); a block that sees a peer with
+ *                     a different code leaves without touching data -> Status::kMismatch
+ *   bounded spin      %globaltimer deadline + host-mapped abort word: a dead peer turns
+ *                     into an error code, never into a hung GPU
+ */
+#ifndef RABIT_SRC_DEVICE_COLL_COMMON_CUH_
+#define RABIT_SRC_DEVICE_COLL_COMMON_CUH_
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace rabit {
+namespace device {
+
+constexpr int kMaxRanks = 16;
+constexpr int kMaxBlocks = 296;          // 2 resident CTAs on each of 148 SMs
+constexpr int kCtrlBytes = 256 << 10;    // control block at the start of every arena
+constexpr int kVec = 16;                 // bytes moved per thread per access
+
+// kernel exit codes written to the host-mapped status word (0 = fine)
+constexpr int kStOk = 0;
+constexpr int kStMismatch = 1;
+constexpr int kStTimeout = 2;
+constexpr int kStAborted = 3;
+
+/*! \brief layout of the control block (per arena). Row = [block][source rank]. */
+struct Control {
+  unsigned long long entry[2][kMaxBlocks][kMaxRanks];  // entry barrier, double-buffered by epoch parity
+  unsigned long long mid[kMaxBlocks][kMaxRanks];       // second barrier of two-phase kernels
+};
+static_assert(sizeof(Control) <= kCtrlBytes, "control block too small");
+
+/*! \brief everything a collective kernel needs; passed by value */
+struct Params {
+  char *arena[kMaxRanks];     // arena base of every rank as mapped HERE
+  char *mc_arena;             // multicast alias of the arenas (NVLS), or NULL
+  int world;
+  int rank;                   // ignored in emulation (rank = blockIdx.y)
+  int emulate;                // 1: all "ranks" are slices of this grid on one GPU (tests, smoke)
+  unsigned int epoch;         // op counter, same on all ranks
+  unsigned int code[kMaxRanks];   // consensus code (index 0 unless emulating)
+  void *user[kMaxRanks];      // user buffer (index 0 unless emulating)
+  void *keep[kMaxRanks];      // optional second destination = result-cache entry
+  size_t bytes;               // payload bytes
+  size_t stage_bytes;         // capacity of one stage (>= bytes rounded to 16)
+  int root;                   // broadcast
+  size_t slice_begin[kMaxRanks], slice_end[kMaxRanks];  // allgather (index 0 unless emulating)
+  volatile int *abort_flag;   // host-mapped; non-zero = give up
+  int *status;                // host-mapped; first non-zero code wins (per emulated rank: status[r])
+  unsigned long long timeout_ns;
+};
+
+__device__ __forceinline__ Control *CtrlOf(const Params &p, int r) {
+  return reinterpret_cast<Control *>(p.arena[r]);
+}
+__device__ __forceinline__ char *StageOf(const Params &p, int r) {
+  return p.arena[r] + kCtrlBytes + static_cast<size_t>(p.epoch & 1u) * p.stage_bytes;
+}
+__device__ __forceinline__ char *McStage(const Params &p) {
+  return p.mc_arena + kCtrlBytes + static_cast<size_t>(p.epoch & 1u) * p.stage_bytes;
+}
+
+__device__ __forceinline__ unsigned long long GlobalTimer() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+__device__ __forceinline__ void StoreReleaseSys(unsigned long long *addr, unsigned long long v) {
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(addr), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long LoadAcquireSys(const unsigned long long *addr) {
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(addr) : "memory");
+  return v;
+}
+
+/*! \brief 16-byte streaming load that does not pollute L1 */
+__device__ __forceinline__ uint4 LoadVec(const void *ptr) {
+  uint4 v;
+  asm volatile("ld.global.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(ptr));
+  return v;
+}
+__device__ __forceinline__ void StoreVec(void *ptr, const uint4 &v) {
+  asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};"
+               ::"l"(ptr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+/*!
+ * \brief block-level flag barrier with the peers' same-numbered block.
+ *  Every thread must call it. Thread i < world writes `value` into rank i's row (slot = my
+ *  rank) and then waits until rank i has written >= value (compared on the high 32 bits)
+ *  into my row. Returns kStOk, or an error every thread of the block agrees on.
+ * \param row_of  functor: Control* -> pointer to this block's row of kMaxRanks words
+ * \param low32   payload in the low half (consensus code on the entry barrier, else 0)
+ * \param peer_low receives rank i's low half in thread i (only when want_low)
+ */
+template <typename RowOf>
+__device__ __forceinline__ int FlagBarrier(const Params &p, int me, RowOf row_of, unsigned int seq,
+                                           unsigned int low32, bool check_code, int *s_verdict) {
+  __syncthreads();  // all of this block's prior global writes are ordered before the signal
+  const int t = threadIdx.x;
+  if (t == 0) *s_verdict = kStOk;
+  __syncthreads();
+  if (t < p.world) {
+    const unsigned long long mine = (static_cast<unsigned long long>(seq) << 32) | low32;
+    StoreReleaseSys(row_of(CtrlOf(p, t)) + me, mine);
+    const unsigned long long *slot = row_of(CtrlOf(p, me)) + t;
+    const unsigned long long deadline = GlobalTimer() + p.timeout_ns;
+    unsigned long long seen;
+    int verdict = kStOk;
+    unsigned int spins = 0;
+    while (true) {
+      seen = LoadAcquireSys(slot);
+      if (static_cast<unsigned int>(seen >> 32) >= seq) break;
+      if ((++spins & 0x3ff) == 0) {
+        if (*p.abort_flag != 0) { verdict = kStAborted; break; }
+        if (GlobalTimer() > deadline) { verdict = kStTimeout; break; }
+      }
+    }
+    if (verdict == kStOk && check_code && static_cast<unsigned int>(seen >> 32) == seq &&
+        static_cast<unsigned int>(seen) != low32) {
+      verdict = kStMismatch;
+    }
+    if (verdict != kStOk) atomicMax(s_verdict, verdict);
+  }
+  __syncthreads();
+  return *s_verdict;
+}
+
+/*! \brief record the first failure of this (emulated) rank for the host */
+__device__ __forceinline__ void Report(const Params &p, int me, int verdict) {
+  if (threadIdx.x == 0 && verdict != kStOk) {
+    atomicCAS(p.status + (p.emulate ? me : 0), kStOk, verdict);
+  }
+}
+
+// ------------------------------------------------------------------ reduce ops
+struct OpMax { template <typename T> __device__ __forceinline__ static T Apply(T a, T b) { return a < b ? b : a; } };
+struct OpMin { template <typename T> __device__ __forceinline__ static T Apply(T a, T b) { return b < a ? b : a; } };
+struct OpSum { template <typename T> __device__ __forceinline__ static T Apply(T a, T b) { return a + b; } };
+struct OpOr {
+  template <typename T> __device__ __forceinline__ static T Apply(T a, T b) { return a | b; }
+};
+
+/*! \brief acc = OP(acc, v) lane-wise over a 16-byte vector of T */
+template <typename T, typename OP>
+__device__ __forceinline__ void ReduceVec(uint4 *acc, const uint4 &v) {
+  constexpr int kLanes = kVec / sizeof(T);
+  T *a = reinterpret_cast<T *>(acc);
+  const T *b = reinterpret_cast<const T *>(&v);
+#pragma unroll
+  for (int i = 0; i < kLanes; ++i) a[i] = OP::Apply(a[i], b[i]);
+}
+
+// ---------------------------------------------------------- user <-> stage copies
+/*! \brief copy [0, bytes) between a user buffer and a 16-byte aligned stage, tiles of this block only.
+ *  Tile t (kTileVecs vectors) belongs to block (t % gridDim.x). The ragged tail (< 16 B) is
+ *  handled byte-wise by the block that owns the tile it falls into. */
+constexpr int kUnroll = 4;
+
+template <bool kToStage>
+__device__ __forceinline__ void CopyTiles(char *user, char *stage, size_t bytes, bool user_aligned) {
+  const size_t nvec = bytes / kVec;
+  const size_t tile_vecs = static_cast<size_t>(blockDim.x) * kUnroll;
+  const size_t ntiles = (nvec + tile_vecs - 1) / tile_vecs;
+  for (size_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const size_t v0 = tile * tile_vecs + threadIdx.x;
+    if (user_aligned) {
+      uint4 r[kUnroll];
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        const size_t v = v0 + static_cast<size_t>(u) * blockDim.x;
+        if (v < nvec) r[u] = LoadVec((kToStage ? user : stage) + v * kVec);
+      }
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        const size_t v = v0 + static_cast<size_t>(u) * blockDim.x;
+        if (v < nvec) StoreVec((kToStage ? stage : user) + v * kVec, r[u]);
+      }
+    } else {
+      // unaligned user pointer: byte granularity on the user side
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        const size_t v = v0 + static_cast<size_t>(u) * blockDim.x;
+        if (v < nvec) {
+          for (int k = 0; k < kVec; ++k) {
+            if (kToStage) stage[v * kVec + k] = user[v * kVec + k];
+            else user[v * kVec + k] = stage[v * kVec + k];
+          }
+        }
+      }
+    }
+  }
+  // ragged tail
+  const size_t tail0 = nvec * kVec;
+  if (tail0 < bytes) {
+    const size_t tail_tile = ntiles == 0 ? 0 : (nvec / tile_vecs);
+    if (tail_tile % gridDim.x == blockIdx.x) {
+      for (size_t i = tail0 + threadIdx.x; i < bytes; i += blockDim.x) {
+        if (kToStage) stage[i] = user[i]; else user[i] = stage[i];
+      }
+    }
+  }
+}
+
+}  // namespace device
+}  // namespace rabit
+#endif  // RABIT_SRC_DEVICE_COLL_COMMON_CUH_

@@ -67,6 +67,22 @@ void HostComm::CloseLinks() {
   ring_prev_ = ring_next_ = nullptr;
 }
 
+bool HostComm::LinksBroken() {
+  for (Link &l : links_) {
+    if (l.sock.IsClosed()) return true;
+    pollfd pf; pf.fd = l.sock.fd; pf.events = POLLIN | POLLRDHUP; pf.revents = 0;
+    if (poll(&pf, 1, 0) <= 0) continue;
+    if (pf.revents & (POLLERR | POLLHUP | POLLRDHUP | POLLNVAL)) return true;
+    if (pf.revents & POLLIN) {
+      char c;
+      ssize_t n = recv(l.sock.fd, &c, 1, MSG_PEEK | MSG_DONTWAIT);
+      if (n == 0) return true;
+      if (n < 0 && !WouldBlock()) return true;
+    }
+  }
+  return false;
+}
+
 Link *HostComm::FindLink(int r) {
   for (Link &l : links_) if (l.rank == r) return &l;
   return nullptr;

@@ -66,6 +66,12 @@ class HostComm {
   bool Connect(const char *cmd);
   /*! \brief drop every peer connection (peers see it as our failure and follow suit) */
   void CloseLinks();
+  /*!
+   * \brief non-blocking health probe of every peer link: true if any peer closed or reset its
+   *  end. The device backend calls this while a kernel is spinning on a peer's flag, so that a
+   *  dead process becomes an abort of the kernel within milliseconds.
+   */
+  bool LinksBroken();
   /*! \brief tell the tracker this rank is done */
   void SendShutdown();
   /*! \brief log line on the tracker, or stdout without one */

@@ -1,0 +1,121 @@
+"""Multi-process tests of the host engine over loopback TCP: guide programs (BASELINE config 1)
+and the reference's fault-injection matrix (test/test.mk:15-37) with our tracker + launcher."""
+import re
+
+import pytest
+
+from conftest import bin_path, run_job
+
+
+def _lines(res):
+    out = []
+    for i in sorted(res.outputs):
+        out.extend(res.outputs[i].splitlines())
+    return out
+
+
+def test_basic_world4_oracle():
+    res = run_job([bin_path("basic")], 4)
+    assert res.ok, res.outputs
+    lines = _lines(res)
+    assert sum("after-allreduce-max: a={3, 4, 5}" in l for l in lines) == 4
+    assert sum("after-allreduce-sum: a={12, 16, 20}" in l for l in lines) == 4
+
+
+def test_broadcast_world3():
+    res = run_job([bin_path("broadcast")], 3)
+    assert res.ok
+    assert sum('after-broadcast: s="hello world"' in l for l in _lines(res)) == 3
+
+
+def test_lazy_allreduce_prepare_skipped_on_recovery():
+    """doc/guide.md:235-241 of the reference: rank 0 dies at the 2nd op; after the restart its first
+    allreduce is recovered from the peer's cache, so the prepare lambda does NOT run again."""
+    res = run_job([bin_path("lazy_allreduce"), "mock=0,0,1,0"], 2)
+    assert res.ok, res.outputs
+    assert res.attempts[0] == 1 and res.attempts[1] == 0
+    second_life = res.outputs[0].split("Hit Mock Error")[-1]
+    assert "run prepare function" not in second_life
+    assert "after-allreduce-max: a={1, 2, 3}" in second_life
+    assert "after-allreduce-sum: a={2, 4, 6}" in second_life
+
+
+@pytest.mark.parametrize("world", [1, 2, 3, 5, 8])
+def test_model_recover_no_fault(world):
+    res = run_job([bin_path("model_recover"), "1000", "rabit_bootstrap_cache=1"], world)
+    assert res.ok, res.outputs
+    assert res.restarts == 0
+
+
+def test_ring_paths_forced():
+    for mincount in ("1", "10"):
+        res = run_job([bin_path("model_recover"), "10000", "rabit_reduce_ring_mincount=" + mincount], 10)
+        assert res.ok, res.outputs
+
+
+def test_tree_path_large_message_and_small_buffer():
+    res = run_job([bin_path("model_recover"), "50000", "rabit_reduce_ring_mincount=100000000",
+                   "rabit_reduce_buffer=4K"], 6)
+    assert res.ok, res.outputs
+    res = run_job([bin_path("model_recover"), "50000", "rabit_reduce_ring_mincount=1", "rabit_reduce_buffer=4K"], 6)
+    assert res.ok, res.outputs
+
+
+# expected deaths: a key fires only while the rank's restart count equals its 4th field, so e.g.
+# mock=0,1,1,0 never fires once rank 0 has already died at mock=0,0,1,0
+SCENARIOS = {
+    "model_recover": ("model_recover", ["mock=0,0,1,0", "mock=1,1,1,0", "rabit_bootstrap_cache=true",
+                                        "rabit_reduce_ring_mincount=1", "rabit_timeout=true",
+                                        "rabit_timeout_sec=30"], 2),
+    "model_die_same": ("model_recover", ["mock=0,0,1,0", "mock=1,1,1,0", "mock=0,1,1,0", "mock=4,1,1,0",
+                                         "mock=9,1,1,0", "rabit_bootstrap_cache=1"], 4),
+    "model_die_hard": ("model_recover", ["mock=0,0,1,0", "mock=1,1,1,0", "mock=1,1,1,1", "mock=0,1,1,0",
+                                         "mock=4,1,1,0", "mock=9,1,1,0", "mock=8,1,2,0", "mock=4,1,3,0",
+                                         "rabit_bootstrap_cache=1"], 6),
+    "local_recover": ("local_recover", ["mock=0,0,1,0", "mock=1,1,1,0", "mock=0,1,1,0", "mock=4,1,1,0",
+                                        "mock=9,1,1,0", "mock=1,1,1,1"], 5),
+    "lazy_die_hard": ("lazy_recover", ["mock=0,0,1,0", "mock=1,1,1,0", "mock=1,1,1,1", "mock=0,1,1,0",
+                                       "mock=4,1,1,0", "mock=9,1,1,0", "mock=8,1,2,0", "mock=4,1,3,0"], 6),
+    "lazy_die_same": ("lazy_recover", ["mock=0,0,1,0", "mock=1,1,1,0", "mock=0,1,1,0", "mock=4,1,1,0",
+                                       "mock=9,1,1,0"], 4),
+}
+
+
+@pytest.mark.parametrize("name", sorted(SCENARIOS))
+def test_fault_matrix_world10(name):
+    prog, args, deaths = SCENARIOS[name]
+    res = run_job([bin_path(prog), "10000"] + args, 10, timeout=180)
+    assert res.ok, {i: o[-600:] for i, o in res.outputs.items()}
+    assert res.restarts == deaths
+    hits = sum(len(re.findall("terminate called", o)) for o in res.outputs.values())
+    assert hits == deaths  # each death is an uncaught rabit::Error -> abort, like the reference
+    # every rank finished all three versions
+    for i, o in res.outputs.items():
+        assert "iter 2" in o, (i, o[-400:])
+
+
+def test_checkpoint_kill_points():
+    """die exactly at CheckPoint / LazyCheckPoint entry (mock seq = ops issued in the version)"""
+    # model_recover at world 4 issues 1 max + 4 broadcasts(2 ops each) + 1 sum + 1 allgather = 11 ops
+    res = run_job([bin_path("model_recover"), "2000", "mock=2,0,11,0", "mock=0,1,11,0", "rabit_bootstrap_cache=1"], 4)
+    assert res.ok and res.restarts == 2, res.outputs
+    res = run_job([bin_path("local_recover"), "2000", "mock=1,0,10,0", "mock=3,2,10,0"], 4)
+    assert res.ok and res.restarts == 2, res.outputs
+
+
+def test_local_replica_survives_adjacent_deaths():
+    """two ring-adjacent ranks die at the same op: with the default 2 replicas the local model of
+    each is still held by a third rank"""
+    res = run_job([bin_path("local_recover"), "3000", "mock=2,1,1,0", "mock=3,1,1,0"], 6)
+    assert res.ok and res.restarts == 2, res.outputs
+
+
+def test_watchdog_kills_stuck_survivors():
+    """a rank dies and is never restarted: with rabit_timeout the survivors must exit (rc 10) instead
+    of waiting forever (reference only prints)"""
+    res = run_job([bin_path("model_recover"), "100", "mock=1,0,1,0", "rabit_timeout=1", "rabit_timeout_sec=2",
+                   "rabit_bootstrap_cache=1"], 3, max_attempts=0, timeout=60)
+    assert not res.ok
+    assert res.returncodes[1] != 0
+    assert res.returncodes[0] == 10 and res.returncodes[2] == 10
+    assert any("exit due to time out 2 s" in o for o in res.outputs.values())
