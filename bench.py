@@ -1,0 +1,378 @@
+#!/usr/bin/env python
+"""Headline benchmark: speed_test-style allreduce (float32, Sum) through rabit-b200.
+
+    python bench.py --gpus 1 --steps K --warmup W
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
+        --master-port P bench.py --gpus N --steps K --warmup W
+    python bench.py --impl reference --gpus N ...      (the unmodified reference, host TCP engine)
+
+Metric (BASELINE.json: "allreduce/broadcast bus GB/s vs msg size"; definition from the
+reference's test/speed_test.cc:52-69, bytes / mean time):
+  value = N * S / t   aggregate bytes allreduced per second over all N GPUs, S = 256 MiB of
+          float32 per rank (fixed as N grows: weak scaling).  Per-rank algorithm bandwidth is
+          S / t and bus bandwidth is (S / t) * 2 (N-1) / N; both are in the JSON, and `sweep`
+          has the bus-bandwidth curve from 1 KiB to 1 GiB for allreduce and broadcast.
+  A "step" is one in-place allreduce of the S-byte device buffer.  Timed on the device with
+  CUDA events after a barrier + synchronize, max over ranks.  The 256 MiB operands exceed the
+  126 MB L2, so consecutive steps cannot be served from cache.
+  e2e: the public blocking API (rabit.allreduce on a tensor, robust engine with fused consensus
+  and result cache) including the H2D copy of the input from pinned memory and the D2H read of
+  the whole result, every step.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+HEADLINE_BYTES = 256 << 20
+METRIC = "allreduce_f32_sum_aggregate_GBps"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--bytes", type=int, default=HEADLINE_BYTES)
+    ap.add_argument("--no-sweep", action="store_true")
+    ap.add_argument("--algo", default="auto")
+    return ap.parse_args()
+
+
+def dist_env():
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", str(rank)))
+    return rank, world, local
+
+
+class ClockSampler(object):
+    """nvidia-smi clocks/throttle reasons sampled every 200 ms while the timed region runs."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.proc = None
+        self.path = None
+        self.gpu = gpu_index
+
+    def start(self):
+        try:
+            fd, self.path = tempfile.mkstemp(suffix=".csv")
+            os.close(fd)
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
+        except OSError:
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.proc is None:
+            return out
+        self.proc.terminate()
+        try:
+            self.proc.wait(5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, reasons = [], set()
+        try:
+            for line in open(self.path):
+                f = [x.strip() for x in line.split(",")]
+                if len(f) < 8:
+                    continue
+                try:
+                    sm.append(float(f[1]))
+                    out["sm_max_mhz"] = float(f[2])
+                except ValueError:
+                    continue
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[4:8]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+            os.remove(self.path)
+        except OSError:
+            pass
+        if sm:
+            sm.sort()
+            out["sm_mhz"] = sm[len(sm) // 2]
+        out["samples"] = len(sm)
+        out["reasons"] = sorted(reasons)
+        return out
+
+
+def make_store(rank, world):
+    """torchrun's MASTER_ADDR/PORT rendezvous as a key-value store (also used to share the tracker port)."""
+    import datetime
+    import torch.distributed as dist
+    if world == 1:
+        return None
+    return dist.TCPStore(os.environ.get("MASTER_ADDR", "127.0.0.1"), int(os.environ.get("MASTER_PORT", "29500")),
+                         world, rank == 0, timeout=datetime.timedelta(seconds=300), wait_for_workers=True)
+
+
+def start_tracker(rank, world, store):
+    """rank 0 hosts the rabit tracker on a free port and publishes it through the store"""
+    if world == 1:
+        return None, None
+    if rank == 0:
+        from rabit_b200.parallel.tracker import Tracker
+        tr = Tracker(world, host="127.0.0.1").start()
+        store.set("rabit_tracker_port", str(tr.port))
+        return tr, tr.port
+    return None, int(store.get("rabit_tracker_port").decode())
+
+
+def max_over_ranks(rabit, np, value):
+    return float(rabit.allreduce(np.array([value], dtype=np.float64), rabit.MAX)[0])
+
+
+# --------------------------------------------------------------------------- ours
+def run_ours(args):
+    import numpy as np
+    import torch
+    rank, world, local = dist_env()
+    assert world == args.gpus or world == 1, "launch with torchrun --nproc-per-node == --gpus"
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    store = make_store(rank, world)
+    tracker, port = start_tracker(rank, world, store)
+    from rabit_b200 import rabit, torch_binding as rt
+    init_args = ["rabit_device=on", "rabit_device_algo=" + args.algo, "rabit_device_arena=%d" % (2 * (args.bytes + 4096) + (1 << 20))]
+    if world > 1:
+        init_args += ["rabit_tracker_uri=127.0.0.1", "rabit_tracker_port=%d" % port, "rabit_task_id=%d" % rank]
+    else:
+        init_args += ["rabit_device_force=1"]
+    rabit.init(init_args)
+    assert rt.device_active(), "device backend did not come up: " + rt.describe()
+    n = rabit.get_world_size()
+    me = rabit.get_rank()
+    S = args.bytes
+    count = S // 4
+    x = torch.empty(count, dtype=torch.float32, device=dev)
+
+    def fill():
+        # small integers: the float sum is exact, so the check below is bit-exact
+        x.copy_((torch.arange(count, device=dev, dtype=torch.int32) % 131).float() * (me + 1))
+
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()          # streams every 100 ms from here until the e2e section is over
+    # correctness of the timed path, once
+    fill()
+    rt.allreduce_async_(x)
+    rt.synchronize()
+    want = (torch.arange(count, device=dev, dtype=torch.int32) % 131).float() * float(n * (n + 1) // 2)
+    assert torch.equal(x, want), "allreduce result is wrong"
+    del want
+
+    def barrier():
+        rabit.allreduce(np.zeros(1, dtype=np.float32), rabit.SUM)
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        rt.synchronize()
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        rt.synchronize()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / steps
+        barrier()
+        return max_over_ranks(rabit, np, ms)
+
+    fill()
+    launches0 = rt.launch_count()
+    ms = timed(lambda: rt.allreduce_async_(x), args.steps, args.warmup)
+    launches = rt.launch_count() - launches0
+    # launches counted above include the warm-up; report the timed share
+    launches = launches * args.steps // (args.steps + args.warmup)
+
+    # ---- end to end through the public blocking API, host buffer in, host buffer out ----
+    e2e_steps = max(3, min(args.steps, 10))
+    h_in = torch.empty(count, dtype=torch.float32).pin_memory()
+    h_in.copy_((torch.arange(count, dtype=torch.int32) % 131).float() * (me + 1))
+    h_out = torch.empty(count, dtype=torch.float32).pin_memory()
+    d = torch.empty(count, dtype=torch.float32, device=dev)
+
+    def e2e_step():
+        d.copy_(h_in, non_blocking=True)
+        rabit.allreduce(d, rabit.SUM)            # public API: robust engine, fused consensus, cached result
+        h_out.copy_(d, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+
+    for _ in range(2):
+        e2e_step()
+    rabit.checkpoint(0)                          # drop the result cache built so far
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e_step()
+    torch.cuda.synchronize()
+    e2e_ms = max_over_ranks(rabit, np, (time.perf_counter() - t0) * 1e3 / e2e_steps)
+    rabit.checkpoint(0)
+    assert float(h_out[5]) == 5.0 * n * (n + 1) // 2
+    clocks = sampler.stop() if rank == 0 else {}
+
+    # ---- NCCL comparator + message-size sweep ----
+    sweep = []
+    nccl_ms = None
+    if not args.no_sweep:
+        import torch.distributed as dist
+        have_nccl = False
+        if world > 1:
+            try:
+                dist.init_process_group("nccl", store=store, rank=rank, world_size=world)
+                have_nccl = True
+            except Exception as e:  # pylint: disable=broad-except
+                if rank == 0:
+                    print("NCCL comparator unavailable: %r" % e, file=sys.stderr)
+        if have_nccl:
+            nccl_ms = timed_nccl(dist, torch, x, args.steps, args.warmup, rabit, np)
+        sizes = [1 << 10, 16 << 10, 256 << 10, 4 << 20, 64 << 20, S]
+        if S < (1 << 30):
+            sizes.append(1 << 30)
+        big = torch.empty((max(sizes) // 4,), dtype=torch.float32, device=dev) if max(sizes) > S else x
+        for sz in sizes:
+            v = big[:sz // 4]
+            it = 20 if sz <= (4 << 20) else 5
+            row = {"bytes": sz}
+            t = timed(lambda: rt.allreduce_async_(v), it, 3)
+            row["allreduce_us"] = t * 1e3
+            row["allreduce_busbw_GBps"] = sz / (t * 1e-3) / 1e9 * (2.0 * (n - 1) / n)
+            t = timed(lambda: rt.broadcast_async_(v, 0), it, 3)
+            row["broadcast_us"] = t * 1e3
+            row["broadcast_busbw_GBps"] = sz / (t * 1e-3) / 1e9
+            if have_nccl:
+                t = timed_nccl(dist, torch, v, it, 3, rabit, np)
+                row["nccl_allreduce_us"] = t * 1e3
+                row["nccl_allreduce_busbw_GBps"] = sz / (t * 1e-3) / 1e9 * (2.0 * (n - 1) / n)
+                t = timed_nccl(dist, torch, v, it, 3, rabit, np, bcast=True)
+                row["nccl_broadcast_us"] = t * 1e3
+                row["nccl_broadcast_busbw_GBps"] = sz / (t * 1e-3) / 1e9
+            sweep.append(row)
+        if have_nccl:
+            dist.destroy_process_group()
+
+    describe = rt.describe()
+    rabit.finalize()
+    if rank == 0:
+        agg = n * S / (ms * 1e-3) / 1e9
+        out = {
+            "metric": METRIC, "value": agg, "unit": "GB/s", "n_gpus": n, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "fp32", "data": "synthetic",
+            "impl": "ours",
+            "algbw_GBps": S / (ms * 1e-3) / 1e9,
+            "busbw_GBps": S / (ms * 1e-3) / 1e9 * (2.0 * (n - 1) / n),
+            "nvlink_roofline_frac_of_770": (S / (ms * 1e-3) / 1e9 * (2.0 * (n - 1) / n)) / 770.0 if n > 1 else None,
+            "config": {"model": "speed_test allreduce Sum float32 (reference test/speed_test.cc)",
+                       "global_batch": n * S, "seq_len": S, "bytes_per_rank": S, "parallelism": "dp%d" % n,
+                       "l2": "operands (256 MiB) larger than the 126 MB L2",
+                       "timing": "CUDA events, barrier+sync both sides, max over ranks",
+                       "algo": args.algo, "backend": describe},
+            "e2e": {"value": n * S / (e2e_ms * 1e-3) / 1e9, "unit": "GB/s", "ms_per_step": e2e_ms,
+                    "steps": e2e_steps, "h2d_bytes_per_step": S, "d2h_bytes_per_step": S,
+                    "path": "pinned host -> H2D -> rabit.allreduce (robust engine) -> D2H of the full result"},
+            "gpu_launches": int(launches),
+            "clocks": clocks,
+        }
+        if nccl_ms is not None:
+            out["nccl"] = {"ms_per_step": nccl_ms, "busbw_GBps": S / (nccl_ms * 1e-3) / 1e9 * (2.0 * (n - 1) / n)}
+        if sweep:
+            out["sweep"] = sweep
+        print(json.dumps(out), flush=True)
+    if tracker is not None:
+        tracker.join(10)
+        tracker.close()
+
+
+def timed_nccl(dist, torch, t, steps, warmup, rabit, np, bcast=False):
+    fn = (lambda: dist.broadcast(t, 0)) if bcast else (lambda: dist.all_reduce(t))
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    rabit.allreduce(np.zeros(1, dtype=np.float32), rabit.SUM)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return max_over_ranks(rabit, np, e0.elapsed_time(e1) / steps)
+
+
+# ---------------------------------------------------------------------- reference
+def run_reference(args):
+    """The UNMODIFIED reference (sources of /root/reference copied to baseline/_ref by
+    baseline/build_ref.py, compiled against a minimal dmlc header shim) running the same step:
+    rabit::Allreduce<op::Sum>(float*, S/4) on host memory through its own socket engine."""
+    rank, world, _ = dist_env()
+    exe = os.path.join(ROOT, "baseline", "_ref", "bin", "ref_speed")
+    if not os.path.isfile(exe):
+        try:
+            sys.path.insert(0, os.path.join(ROOT, "baseline"))
+            import build_ref
+            build_ref.build()
+        except Exception as e:  # pylint: disable=broad-except
+            if rank == 0:
+                print(json.dumps({"impl": "reference", "unavailable": "reference build failed: %s" % str(e)[:200]}))
+            return
+    if args.gpus == 1 and world == 1:
+        print(json.dumps({"impl": "reference", "unavailable":
+                          "world_size=1: rabit::Allreduce returns immediately (allreduce_robust.cc:253-256), "
+                          "there is no transfer to time"}))
+        return
+    store = make_store(rank, world)
+    tracker, port = start_tracker(rank, world, store)
+    env = dict(os.environ)
+    env.update({"DMLC_TRACKER_URI": "127.0.0.1", "DMLC_TRACKER_PORT": str(port), "DMLC_TASK_ID": str(rank),
+                "DMLC_ROLE": "worker", "DMLC_NUM_ATTEMPT": "0"})
+    steps = max(1, min(args.steps, 5))   # ~1 s per 256 MiB op on loopback TCP
+    warm = max(1, min(args.warmup, 2))
+    r = subprocess.run([exe, str(args.bytes // 4), str(steps), str(warm), "rabit_enable_tcp_no_delay=true"],
+                       env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE, timeout=3000)
+    if tracker is not None:
+        tracker.join(20)
+        tracker.close()
+    if rank == 0:
+        line = [l for l in r.stdout.decode().splitlines() if l.startswith("REF_RESULT")]
+        if r.returncode != 0 or not line:
+            print(json.dumps({"impl": "reference", "unavailable": "reference run failed rc=%d: %s" %
+                              (r.returncode, r.stderr.decode()[-200:])}))
+            return
+        ms = float(line[0].split()[1])
+        n, S = world, args.bytes
+        print(json.dumps({
+            "metric": METRIC, "value": n * S / (ms * 1e-3) / 1e9, "unit": "GB/s", "n_gpus": n, "steps": steps,
+            "warmup": warm, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "fp32", "data": "synthetic", "impl": "reference",
+            "busbw_GBps": S / (ms * 1e-3) / 1e9 * (2.0 * (n - 1) / n),
+            "config": {"model": "speed_test allreduce Sum float32 (reference test/speed_test.cc)",
+                       "bytes_per_rank": S, "parallelism": "dp%d" % n,
+                       "engine": "reference AllreduceRobust over loopback TCP, host memory, rabit_enable_tcp_no_delay=true",
+                       "timing": "host wall clock inside the reference program (it has no device path), max over ranks"},
+            "e2e": {"value": n * S / (ms * 1e-3) / 1e9, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0,
+                    "path": "host buffer in, host buffer out (the reference's only mode)"},
+            "gpu_launches": 0}), flush=True)
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)

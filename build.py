@@ -65,7 +65,7 @@ def find_nvcc():
 def headers():
     hs = []
     for pat in ("include/rabit/*.h", "include/rabit/internal/*.h", "include/*.h", "src/host/*.h",
-                "src/device/*.h", "src/device/*.cuh"):
+                "src/device/*.h", "src/device/*.cuh", "src/device/*.inc"):
         hs += glob.glob(os.path.join(ROOT, pat))
     return hs
 

@@ -144,3 +144,20 @@ def synchronize():
     if rc != 0:
         raise RuntimeError("device collective failed: %s" %
                            {1: "consensus mismatch", 2: "peer timeout", 3: "peer lost"}.get(rc, rc))
+
+
+def set_tuning(algo=None, blocks=0, trace=False):
+    """Runtime override of the allreduce algorithm ('auto', 'oneshot', 'twoshot', 'tma', 'nvls'),
+    the block cap (0 = default) and the phase trace (see :func:`get_trace`)."""
+    lib = _lib()
+    lib.RabitDeviceSetTuning.argtypes = [ctypes.c_char_p, ctypes.c_int, ctypes.c_int]
+    lib.RabitDeviceSetTuning(None if algo is None else algo.encode(), int(blocks), int(bool(trace)))
+
+
+def get_trace():
+    """Phase timestamps (ns, %globaltimer) of block 0 of the last traced kernel:
+    [start, staged, entry barrier passed, reduce-scatter done, mid barrier passed, end]."""
+    lib = _lib()
+    out = (ctypes.c_ulonglong * 6)()
+    lib.RabitDeviceGetTrace(out)
+    return list(out)

@@ -42,6 +42,8 @@ constexpr int kStAborted = 3;
 struct Control {
   unsigned long long entry[2][kMaxBlocks][kMaxRanks];  // entry barrier, double-buffered by epoch parity
   unsigned long long mid[kMaxBlocks][kMaxRanks];       // second barrier of two-phase kernels
+  unsigned long long pipe_a[kMaxBlocks][kMaxRanks];    // pipelined kernel: rounds staged by rank r
+  unsigned long long pipe_b[kMaxBlocks][kMaxRanks];    // pipelined kernel: rounds reduced by rank r
 };
 static_assert(sizeof(Control) <= kCtrlBytes, "control block too small");
 
@@ -63,6 +65,7 @@ struct Params {
   volatile int *abort_flag;   // host-mapped; non-zero = give up
   int *status;                // host-mapped; first non-zero code wins (per emulated rank: status[r])
   unsigned long long timeout_ns;
+  unsigned long long *trace;  // optional host-mapped phase timestamps of block 0 (NULL = off)
 };
 
 __device__ __forceinline__ Control *CtrlOf(const Params &p, int r) {
@@ -148,6 +151,11 @@ __device__ __forceinline__ void Report(const Params &p, int me, int verdict) {
   if (threadIdx.x == 0 && verdict != kStOk) {
     atomicCAS(p.status + (p.emulate ? me : 0), kStOk, verdict);
   }
+}
+
+/*! \brief phase timestamp (block 0 / thread 0 only) for the tuning tools; no-op unless enabled */
+__device__ __forceinline__ void Stamp(const Params &p, int idx) {
+  if (p.trace != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) p.trace[idx] = GlobalTimer();
 }
 
 // ------------------------------------------------------------------ reduce ops

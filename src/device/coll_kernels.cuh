@@ -66,9 +66,12 @@ __global__ void __launch_bounds__(512) OneShotAllreduce(Params p) {
   char *user = static_cast<char *>(p.user[p.emulate ? me : 0]);
   char *keep = static_cast<char *>(p.keep[p.emulate ? me : 0]);
   const bool aligned = (reinterpret_cast<uintptr_t>(user) % kVec) == 0;
+  Stamp(p, 0);
   CopyTiles<true>(user, StageOf(p, me), p.bytes, aligned);
+  Stamp(p, 1);
   int verdict = FlagBarrier(p, me, EntryRow{p.epoch & 1u}, p.epoch + 1, p.code[p.emulate ? me : 0], true, &s_verdict);
   if (verdict != kStOk) { Report(p, me, verdict); return; }
+  Stamp(p, 2);
 
   const size_t nvec_full = p.bytes / kVec;
   const size_t nvec = (p.bytes + kVec - 1) / kVec;
@@ -103,6 +106,7 @@ __global__ void __launch_bounds__(512) OneShotAllreduce(Params p) {
       if (v < nvec) Emit(user, keep, v, nvec_full, p.bytes, acc[u], aligned);
     }
   }
+  Stamp(p, 5);
 }
 
 template <typename T, typename OP>
@@ -112,9 +116,12 @@ __global__ void __launch_bounds__(512) TwoShotAllreduce(Params p) {
   char *user = static_cast<char *>(p.user[p.emulate ? me : 0]);
   char *keep = static_cast<char *>(p.keep[p.emulate ? me : 0]);
   const bool aligned = (reinterpret_cast<uintptr_t>(user) % kVec) == 0;
+  Stamp(p, 0);
   CopyTiles<true>(user, StageOf(p, me), p.bytes, aligned);
+  Stamp(p, 1);
   int verdict = FlagBarrier(p, me, EntryRow{p.epoch & 1u}, p.epoch + 1, p.code[p.emulate ? me : 0], true, &s_verdict);
   if (verdict != kStOk) { Report(p, me, verdict); return; }
+  Stamp(p, 2);
 
   const size_t nvec_full = p.bytes / kVec;
   const size_t nvec = (p.bytes + kVec - 1) / kVec;
@@ -152,8 +159,10 @@ __global__ void __launch_bounds__(512) TwoShotAllreduce(Params p) {
       if (v < nvec) StoreVec(my_stage + v * kVec, acc[u]);
     }
   }
+  Stamp(p, 3);
   verdict = FlagBarrier(p, me, MidRow{}, p.epoch + 1, 0u, false, &s_verdict);
   if (verdict != kStOk) { Report(p, me, verdict); return; }
+  Stamp(p, 4);
   // allgather: pull every tile from its owner's stage
   for (size_t tile = blockIdx.x, k = 0; tile < ntiles; tile += gridDim.x, ++k) {
     const char *src = StageOf(p, static_cast<int>(k % n));
@@ -170,6 +179,7 @@ __global__ void __launch_bounds__(512) TwoShotAllreduce(Params p) {
       if (v < nvec) Emit(user, keep, v, nvec_full, p.bytes, r[u], aligned);
     }
   }
+  Stamp(p, 5);
 }
 
 /*! \brief root stages its buffer; everyone (root included, for the cache copy) pulls it */

@@ -86,9 +86,12 @@ __global__ void __launch_bounds__(512) NvlsAllreduce(Params p) {
   char *user = static_cast<char *>(p.user[0]);
   char *keep = static_cast<char *>(p.keep[0]);
   const bool aligned = (reinterpret_cast<uintptr_t>(user) % kVec) == 0;
+  Stamp(p, 0);
   CopyTiles<true>(user, StageOf(p, me), p.bytes, aligned);
+  Stamp(p, 1);
   int verdict = FlagBarrier(p, me, EntryRow{p.epoch & 1u}, p.epoch + 1, p.code[0], true, &s_verdict);
   if (verdict != kStOk) { Report(p, me, verdict); return; }
+  Stamp(p, 2);
   const size_t nvec_full = p.bytes / kVec;
   const size_t nvec = (p.bytes + kVec - 1) / kVec;
   const size_t tile_vecs = static_cast<size_t>(blockDim.x) * kUnroll;
@@ -110,8 +113,10 @@ __global__ void __launch_bounds__(512) NvlsAllreduce(Params p) {
       if (v < nvec) MultimemStore(mc_stage + v * kVec, acc[u]);
     }
   }
+  Stamp(p, 3);
   verdict = FlagBarrier(p, me, MidRow{}, p.epoch + 1, 0u, false, &s_verdict);
   if (verdict != kStOk) { Report(p, me, verdict); return; }
+  Stamp(p, 4);
   // every tile of this channel now sits, fully reduced, in OUR stage: local copy-out
   const char *src = StageOf(p, me);
   for (size_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
@@ -128,6 +133,7 @@ __global__ void __launch_bounds__(512) NvlsAllreduce(Params p) {
       if (v < nvec) Emit(user, keep, v, nvec_full, p.bytes, r[u], aligned);
     }
   }
+  Stamp(p, 5);
 }
 
 /*! \brief root: user -> multicast store into everybody's stage; all: barrier, local copy-out */

@@ -61,9 +61,12 @@ __global__ void __launch_bounds__(kTmaThreads) TwoShotAllreduceTma(Params p, int
     for (int s = 0; s < depth; ++s) MbarInit(&full[s], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
+  Stamp(p, 0);
   CopyTiles<true>(user, StageOf(p, me), p.bytes, aligned);
+  Stamp(p, 1);
   int verdict = FlagBarrier(p, me, EntryRow{p.epoch & 1u}, p.epoch + 1, p.code[p.emulate ? me : 0], true, &s_verdict);
   if (verdict != kStOk) { Report(p, me, verdict); return; }
+  Stamp(p, 2);
 
   const size_t nvec_full = p.bytes / kVec;
   const size_t nvec = (p.bytes + kVec - 1) / kVec;
@@ -116,8 +119,10 @@ __global__ void __launch_bounds__(kTmaThreads) TwoShotAllreduceTma(Params p, int
     }
     __syncthreads();
   }
+  Stamp(p, 3);
   verdict = FlagBarrier(p, me, MidRow{}, p.epoch + 1, 0u, false, &s_verdict);
   if (verdict != kStOk) { Report(p, me, verdict); return; }
+  Stamp(p, 4);
   const size_t tile_vecs = static_cast<size_t>(blockDim.x) * kUnroll;
   for (size_t tile = blockIdx.x, k = 0; tile < ntiles; tile += gridDim.x, ++k) {
     const char *src = StageOf(p, static_cast<int>(k % n));
@@ -134,6 +139,7 @@ __global__ void __launch_bounds__(kTmaThreads) TwoShotAllreduceTma(Params p, int
       if (v < nvec) Emit(user, keep, v, nvec_full, p.bytes, r[u], aligned);
     }
   }
+  Stamp(p, 5);
 }
 
 /*! \brief dynamic shared memory the TMA kernel needs for a given world and depth */

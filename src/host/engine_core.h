@@ -14,6 +14,7 @@
 #define RABIT_SRC_HOST_ENGINE_CORE_H_
 
 #include <atomic>
+#include <functional>
 #include <map>
 #include <memory>
 #include <string>
@@ -222,7 +223,8 @@ class RobustEngine : public BaseEngine {
    *  (barrier passed, or `buf` filled with the cached result), false when the caller must
    *  now execute the step itself.
    */
-  bool Consensus(void *buf, size_t size, uint32_t flags, uint32_t seq);
+  bool Consensus(void *buf, size_t size, uint32_t flags, uint32_t seq,
+                 const std::function<void *()> *lazy_buf = nullptr);
   /*! \brief failure handler: kOk -> true; otherwise tear down, re-rendezvous, return false */
   bool Healthy(Status s);
   void StartWatchdog();
@@ -253,6 +255,8 @@ class RobustEngine : public BaseEngine {
   ResultStore results_;
   std::vector<std::pair<std::string, std::string> > boot_cache_;  // key -> result, insertion order
   bool checkpoint_loaded_ = false;
+  /*! \brief all ranks are known to be at the same op: device collectives may use the fused kernel path */
+  bool in_sync_ = false;
   std::string global_blob_;                  // [int32 version][Save bytes]
   const Serializable *lazy_model_ = nullptr;
   // local models: slot j holds the blob of rank (me - j); two generations

@@ -43,51 +43,60 @@ void RobustEngine::RunOp(OpArgs *a) {
 
   // device buffers whose op the kernels cannot express go through a host mirror
   const bool fused = on_device && (a->kind != OpKind::kAllreduce || (a->dtype >= 0 && a->op >= 0));
+  // (allocated only when the host protocol actually has to look at the bytes)
   std::string mirror;
   char *view = static_cast<char *>(a->buf);
-  if (on_device) { mirror.resize(a->bytes); view = &mirror[0]; }
+  auto need_view = [&]() {
+    if (on_device && mirror.size() != a->bytes) { mirror.resize(a->bytes); view = &mirror[0]; }
+  };
+  if (on_device) view = nullptr;
 
-  bool prepared = false, recovered = false, done = false;
+  bool prepared = false, recovered = false;
   auto prepare_once = [&]() {
     if (!prepared && a->prepare_fun != nullptr) a->prepare_fun(a->prepare_arg);
     prepared = true;
   };
 
+  if (boot) need_view();
   if (boot && BootLookup(a->key, view, a->bytes)) {
     if (on_device) device_->CopyH2D(a->buf, view, a->bytes);
     return;
   }
 
   char *slot = nullptr;
-  if (fused && !boot) {
-    // Fast path: ONE kernel does consensus + transfer + reduce + the cache copy. It only falls
-    // back to the host protocol when the ranks disagree or a peer is gone.
-    const uint32_t code = proto::Request{static_cast<uint32_t>(seq_), 0, 0}.Code();
-    prepare_once();
-    void *keep = results_.AllocTempDevice(a->bytes);
-    Status st = Status::kOk;
-    switch (a->kind) {
-      case OpKind::kAllreduce:
-        st = device_->Allreduce(a->buf, a->bytes / DTypeBytes(a->dtype), a->dtype, a->op, 1, code, keep);
+  bool dropped = false;
+  const bool use_kernel = fused && !boot;
+  while (true) {
+    if (use_kernel && in_sync_) {
+      // Fast path: ONE kernel does consensus + transfer + reduce + the cache copy. It is only
+      // attempted while this rank has reason to believe everybody is at the same op; it falls
+      // back to the host protocol when the ranks disagree or a peer is gone.
+      const uint32_t code = proto::Request{static_cast<uint32_t>(seq_), 0, 0}.Code();
+      prepare_once();
+      void *keep = results_.AllocTempDevice(a->bytes);
+      Status st = Status::kOk;
+      switch (a->kind) {
+        case OpKind::kAllreduce:
+          st = device_->Allreduce(a->buf, a->bytes / DTypeBytes(a->dtype), a->dtype, a->op, 1, code, keep);
+          break;
+        case OpKind::kBroadcast: st = device_->Broadcast(a->buf, a->bytes, a->root, code, keep); break;
+        case OpKind::kAllgather:
+          st = device_->Allgather(a->buf, a->bytes, a->slice_begin, a->slice_end, code, keep);
+          break;
+      }
+      if (Ok(st)) {
+        // consensus passed inside the kernel: the previous result may go
+        if (!dropped) { DropStaleResult(); dropped = true; }
         break;
-      case OpKind::kBroadcast: st = device_->Broadcast(a->buf, a->bytes, a->root, code, keep); break;
-      case OpKind::kAllgather:
-        st = device_->Allgather(a->buf, a->bytes, a->slice_begin, a->slice_end, code, keep);
-        break;
-    }
-    if (Ok(st)) {
-      DropStaleResult();  // consensus passed inside the kernel: the previous result may go
-      done = true;
-    } else {
+      }
       results_.DiscardTemp();
-      // kMismatch: somebody is elsewhere in the protocol. Anything else: a peer is gone —
-      // tear down and re-join. Either way the host protocol below decides what happens next.
+      in_sync_ = false;
+      // kMismatch: somebody is elsewhere in the protocol. Anything else: a peer is gone, tear down
+      // and re-join. Either way the host protocol decides what happens next.
       if (st != Status::kMismatch) Healthy(st);
     }
-  }
-
-  if (!done) {
-    recovered = Consensus(view, a->bytes, flags, static_cast<uint32_t>(seq_));
+    const std::function<void *()> lazy = [&]() -> void * { need_view(); return view; };
+    recovered = Consensus(view, a->bytes, flags, static_cast<uint32_t>(seq_), &lazy);
     if (boot && recovered) {
       // the cache was just restored from a peer: this op must be in it
       utils::Check(BootLookup(a->key, view, a->bytes),
@@ -95,19 +104,27 @@ void RobustEngine::RunOp(OpArgs *a) {
       if (on_device) device_->CopyH2D(a->buf, view, a->bytes);
       return;
     }
-    DropStaleResult();
-    if (!recovered) prepare_once();
-    slot = results_.AllocTemp(a->bytes);
-    while (!recovered) {
-      if (on_device) device_->CopyD2H(view, a->buf, a->bytes);
+    if (!dropped) { DropStaleResult(); dropped = true; }
+    if (recovered) {
+      slot = results_.AllocTemp(a->bytes);
       std::memcpy(slot, view, a->bytes);
-      // the transfer works on the cache slot so that a failure half-way leaves the caller's
-      // buffer intact for the retry
-      if (Healthy(TryOp(*a, slot))) { std::memcpy(view, slot, a->bytes); break; }
-      recovered = Consensus(view, a->bytes, flags, static_cast<uint32_t>(seq_));
+      if (on_device) device_->CopyH2D(a->buf, view, a->bytes);
+      break;
     }
-    if (recovered) std::memcpy(slot, view, a->bytes);
-    if (on_device) device_->CopyH2D(a->buf, view, a->bytes);
+    in_sync_ = true;  // the consensus round just said: every rank is about to run this very op
+    if (use_kernel) continue;
+    need_view();
+    prepare_once();
+    slot = results_.AllocTemp(a->bytes);
+    if (on_device) device_->CopyD2H(view, a->buf, a->bytes);
+    std::memcpy(slot, view, a->bytes);
+    // the transfer works on the cache slot so that a failure half-way leaves the caller's buffer
+    // intact for the retry
+    if (Healthy(TryOp(*a, slot))) {
+      std::memcpy(view, slot, a->bytes);
+      if (on_device) device_->CopyH2D(a->buf, view, a->bytes);
+      break;
+    }
   }
 
   if (comm_.cfg.debug) {

@@ -103,6 +103,7 @@ void RobustEngine::StopWatchdog() {
 bool RobustEngine::Healthy(Status s) {
   if (Ok(s)) { StopWatchdog(); return true; }
   ++recover_counter_;
+  in_sync_ = false;
   if (comm_.cfg.debug) {
     utils::HandleLogInfo("[%d] link failure (%s) at version %d seq %d, re-joining\n", comm_.rank,
                          StatusName(s), version_number_, seq_);
@@ -121,7 +122,8 @@ bool RobustEngine::Healthy(Status s) {
 }
 
 // ----------------------------------------------------------------- consensus
-bool RobustEngine::Consensus(void *buf, size_t size, uint32_t flags, uint32_t seq) {
+bool RobustEngine::Consensus(void *buf, size_t size, uint32_t flags, uint32_t seq,
+                             const std::function<void *()> *lazy_buf) {
   Request me{seq, flags, static_cast<uint32_t>(boot_cache_.size())};
   while (true) {
     this->ReportStatus();
@@ -147,6 +149,9 @@ bool RobustEngine::Consensus(void *buf, size_t size, uint32_t flags, uint32_t se
         if (Healthy(ServeCache(v.requester, sum.max_cache)) && v.requester) return true;
         break;
       case proto::kServeResult:
+        // the landing buffer of a requester may be expensive (host mirror of a device tensor):
+        // it is only materialised when this rank really is about to receive
+        if (v.requester && buf == nullptr && lazy_buf != nullptr) buf = (*lazy_buf)();
         if (Healthy(ServeResult(buf, size, sum.min_seq, v.requester)) && v.requester) return true;
         break;
     }

@@ -1,0 +1,85 @@
+"""Self-checking device-buffer workload, one process per GPU (launched by test_gpu_multi.py).
+
+The GPU twin of test/model_recover.cc: every collective runs on CUDA tensors through the
+public API (robust engine -> fused kernels), results are compared with closed forms, the
+model is checkpointed every iteration, and `mock=rank,version,seq,trial` kills ranks so
+that LoadCheckPoint + result-cache replay are exercised on device buffers.
+usage: gpu_worker.py <ndata> [iters=N] [mock=...] [rabit_*=...]
+"""
+import os
+import sys
+
+import numpy as np
+import torch
+
+from rabit_b200 import rabit
+from rabit_b200 import torch_binding as rt
+
+
+def contribution(n, r, it, mod, dev):
+    i = torch.arange(n, device=dev, dtype=torch.int64)
+    return ((i * (r + 1) + it) % mod).float()
+
+
+def main():
+    n = int(sys.argv[1])
+    iters = 3
+    for a in sys.argv[2:]:
+        if a.startswith("iters="):
+            iters = int(a[6:])
+    ordinal = int(os.environ.get("RABIT_DEVICE_ORDINAL", os.environ.get("RABIT_LOCAL_RANK", "0")))
+    torch.cuda.set_device(ordinal % torch.cuda.device_count())
+    dev = torch.device("cuda", torch.cuda.current_device())
+    rabit.init(sys.argv, lib="mock")
+    me, world = rabit.get_rank(), rabit.get_world_size()
+    assert rt.device_active(), rt.describe()
+    version, model = rabit.load_checkpoint()
+    if version == 0:
+        model = np.ones(n, dtype=np.float32)
+    model = torch.from_numpy(model).to(dev)
+    print("[%d] start at iter=%d on %s | %s" % (me, version, dev, rt.describe()), flush=True)
+    for it in range(version, iters):
+        # max with lazy prepare
+        x = torch.empty(n, device=dev)
+
+        def fill(t):
+            t.copy_(contribution(n, me, it, 97 + it, dev) + model)
+        rabit.allreduce(x, rabit.MAX, fill)
+        want = torch.stack([contribution(n, r, it, 97 + it, dev) + model for r in range(world)]).max(0).values
+        assert torch.equal(x, want), "[%d] max mismatch iter %d" % (me, it)
+        # broadcast bytes from a rotating root
+        root = it % world
+        b = torch.full((n,), 255, dtype=torch.uint8, device=dev)
+        truth = ((torch.arange(n, device=dev) * 7 + root + it) % 251).to(torch.uint8)
+        if me == root:
+            b.copy_(truth)
+        rt.broadcast_(b, root)
+        assert torch.equal(b, truth), "[%d] broadcast mismatch iter %d" % (me, it)
+        # sum
+        y = contribution(n, me, it, 113 + it, dev) + x
+        rabit.allreduce(y, rabit.SUM)
+        want = torch.stack([contribution(n, r, it, 113 + it, dev) + x for r in range(world)]).sum(0)
+        assert torch.equal(y, want), "[%d] sum mismatch iter %d" % (me, it)
+        # grad/hess pair histogram: float64 sum over 2x elements
+        h = (contribution(2 * 256, me, it, 89, dev).double() + 0.5)
+        rabit.allreduce(h, rabit.SUM)
+        want = torch.stack([contribution(2 * 256, r, it, 89, dev).double() + 0.5 for r in range(world)]).sum(0)
+        assert torch.equal(h, want), "[%d] pair-sum mismatch iter %d" % (me, it)
+        # allgather
+        per = 33
+        g = torch.zeros(per * world, dtype=torch.int32, device=dev)
+        g[me * per:(me + 1) * per] = me * 1000 + it
+        rt.allgather_(g, me * per, per)
+        want = torch.arange(world, device=dev, dtype=torch.int32).repeat_interleave(per) * 1000 + it
+        assert torch.equal(g, want), "[%d] allgather mismatch iter %d" % (me, it)
+        model = y % 1000.0
+        rabit.checkpoint(model.cpu().numpy())
+        print("[%d] iter %d checkpointed (version %d)" % (me, it, rabit.version_number()), flush=True)
+    launches = rt.launch_count()
+    rabit.tracker_print("[%d] done, %d kernel launches\n" % (me, launches))
+    assert launches > 0
+    rabit.finalize()
+
+
+if __name__ == "__main__":
+    main()

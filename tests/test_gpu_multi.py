@@ -1,0 +1,50 @@
+"""Multi-GPU tests: one process per GPU, real peer memory (needs >= 2 GPUs; skipped otherwise).
+
+Covers BASELINE config 4 (checkpoint + result-cache replay after mock kills, on device buffers).
+"""
+import os
+import sys
+
+import pytest
+
+from conftest import ROOT, run_job
+
+pytestmark = pytest.mark.gpu
+
+
+def _ngpu():
+    import torch
+    return torch.cuda.device_count() if torch.cuda.is_available() else 0
+
+
+def _run(args, n, timeout=300, **kw):
+    env = {"PYTHONPATH": ROOT + os.pathsep + os.environ.get("PYTHONPATH", ""), "RABIT_DEVICE_VERBOSE": "1"}
+    return run_job([sys.executable, os.path.join(ROOT, "tests", "gpu_worker.py")] + args, n, timeout=timeout,
+                   env=env, per_rank_gpu=True, **kw)
+
+
+@pytest.fixture(scope="module")
+def world():
+    n = _ngpu()
+    if n < 2:
+        pytest.skip("needs at least 2 GPUs")
+    return min(n, 8)
+
+
+@pytest.mark.parametrize("algo", ["auto", "oneshot", "twoshot", "tma"])
+def test_device_collectives_no_fault(world, algo):
+    res = _run(["200000", "rabit_device_algo=" + algo], world)
+    assert res.ok, {i: o[-1500:] for i, o in res.outputs.items()}
+    assert res.restarts == 0
+    assert any("kernel launches" in m for m in res.messages)
+
+
+def test_device_recovery_after_kills(world):
+    """a rank dies in version 0 and another in version 1; both come back, load the checkpoint and
+    replay the cached device results"""
+    res = _run(["50000", "mock=0,0,1,0", "mock=1,1,2,0", "rabit_timeout=1", "rabit_timeout_sec=120"], world,
+               timeout=600)
+    assert res.ok, {i: o[-2500:] for i, o in res.outputs.items()}
+    assert res.restarts == 2
+    for i, o in res.outputs.items():
+        assert "iter 2 checkpointed" in o
