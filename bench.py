@@ -348,8 +348,16 @@ def run_reference(args):
     if tracker is not None:
         tracker.join(20)
         tracker.close()
+    # rabit rank 0 (the one that prints) is whatever process the tracker labelled 0: route its line to
+    # torchrun rank 0 through the store
+    mine = [l for l in r.stdout.decode().splitlines() if l.startswith("REF_RESULT")]
+    if mine:
+        store.set("ref_result", mine[0])
+    store.set("ref_rc_%d" % rank, str(r.returncode))
     if rank == 0:
-        line = [l for l in r.stdout.decode().splitlines() if l.startswith("REF_RESULT")]
+        line = []
+        if all(store.get("ref_rc_%d" % q).decode() == "0" for q in range(world)):
+            line = [store.get("ref_result").decode()]
         if r.returncode != 0 or not line:
             print(json.dumps({"impl": "reference", "unavailable": "reference run failed rc=%d: %s" %
                               (r.returncode, r.stderr.decode()[-200:])}))

@@ -26,6 +26,7 @@ def main():
     ap.add_argument("--blocks", default="0")
     ap.add_argument("--iters", type=int, default=10)
     ap.add_argument("--out", default="")
+    ap.add_argument("--sym", action="store_true", help="operate on a symmetric (zero-copy) buffer")
     args = ap.parse_args()
     rank, world, local = bench.dist_env()
     torch.cuda.set_device(local)
@@ -34,13 +35,19 @@ def main():
     tracker, port = bench.start_tracker(rank, world, store)
     sizes = [int(s) for s in args.sizes.split(",")]
     init = ["rabit_device=on", "rabit_device_arena=%d" % (2 * max(sizes) + (4 << 20))]
+    if args.sym:
+        init += ["rabit_device_heap=%d" % (max(sizes) + (1 << 20))]
     if world > 1:
         init += ["rabit_tracker_uri=127.0.0.1", "rabit_tracker_port=%d" % port, "rabit_task_id=%d" % rank]
     else:
         init += ["rabit_device_force=1"]
     rabit.init(init)
     n = rabit.get_world_size()
-    x = torch.zeros(max(sizes) // 4, dtype=torch.float32, device=dev)
+    me = rabit.get_rank()
+    if args.sym:
+        x = rt.symmetric_empty(max(sizes) // 4, torch.float32)
+    else:
+        x = torch.zeros(max(sizes) // 4, dtype=torch.float32, device=dev)
     rows = []
     for sz in sizes:
         v = x[:sz // 4]
@@ -49,6 +56,16 @@ def main():
                 continue
             for blocks in [int(b) for b in args.blocks.split(",")]:
                 rt.set_tuning(algo, blocks, trace=False)
+                # correctness first: small integers, exact in fp32
+                v.copy_((torch.arange(v.numel(), device=dev, dtype=torch.int32) % 61).float() * (me + 1))
+                rabit.allreduce(np.zeros(1, dtype=np.float32), rabit.SUM)
+                torch.cuda.synchronize()
+                rt.allreduce_async_(v)
+                rt.synchronize()
+                want = (torch.arange(v.numel(), device=dev, dtype=torch.int32) % 61).float() * float(n * (n + 1) // 2)
+                ok = bool(torch.equal(v, want))
+                del want
+                v.zero_()
                 for _ in range(3):
                     rt.allreduce_async_(v)
                 rt.synchronize()
@@ -67,7 +84,7 @@ def main():
                 rt.synchronize()
                 tr = rt.get_trace()
                 ph = [(tr[i + 1] - tr[i]) / 1e3 if tr[i + 1] >= tr[i] else -1 for i in range(5)]
-                row = {"bytes": sz, "algo": algo, "blocks": blocks, "us": ms * 1e3,
+                row = {"bytes": sz, "algo": ("sym-" if args.sym else "") + algo, "blocks": blocks, "correct": ok, "us": ms * 1e3,
                        "busbw_GBps": sz / (ms * 1e-3) / 1e9 * 2 * (n - 1) / max(n, 1),
                        "phases_us(stage,barrierA,rs,barrierB,ag)": [round(p, 1) for p in ph]}
                 rows.append(row)

@@ -161,3 +161,32 @@ def get_trace():
     out = (ctypes.c_ulonglong * 6)()
     lib.RabitDeviceGetTrace(out)
     return list(out)
+
+
+class _SymBlock(object):
+    """CUDA-array-interface view of a piece of the symmetric heap (keeps nothing alive: the heap
+    belongs to the engine and lives until finalize())."""
+
+    def __init__(self, ptr, numel, dtype):
+        typestr = {torch.float32: "<f4", torch.float64: "<f8", torch.int32: "<i4", torch.int64: "<i8",
+                   torch.uint8: "|u1", torch.int8: "|i1"}[dtype]
+        self.__cuda_array_interface__ = {"shape": (numel,), "typestr": typestr, "data": (ptr, False),
+                                         "version": 2, "strides": None}
+
+
+def symmetric_empty(numel, dtype=torch.float32, device=None):
+    """A 1-D CUDA tensor inside the engine's symmetric heap (``rabit_device_heap=<bytes>`` at init).
+
+    Collective: every rank must allocate the same sizes in the same order.  Collectives on such a
+    tensor are zero-copy (peers address it directly over NVLink / through the multicast mapping).
+    """
+    lib = _lib()
+    lib.RabitDeviceSymAlloc.restype = ctypes.c_void_p
+    lib.RabitDeviceSymAlloc.argtypes = [ctypes.c_size_t]
+    nbytes = numel * torch.empty((), dtype=dtype).element_size()
+    ptr = lib.RabitDeviceSymAlloc(nbytes)
+    if not ptr:
+        raise MemoryError("symmetric heap exhausted or not configured (pass rabit_device_heap=<bytes> to init)")
+    if device is None:
+        device = torch.device("cuda", torch.cuda.current_device())
+    return torch.as_tensor(_SymBlock(ptr, numel, dtype), device=device)

@@ -42,6 +42,7 @@ constexpr int kStAborted = 3;
 struct Control {
   unsigned long long entry[2][kMaxBlocks][kMaxRanks];  // entry barrier, double-buffered by epoch parity
   unsigned long long mid[kMaxBlocks][kMaxRanks];       // second barrier of two-phase kernels
+  unsigned long long exit_[kMaxBlocks][kMaxRanks];     // exit barrier of the in-place kernels
   unsigned long long pipe_a[kMaxBlocks][kMaxRanks];    // pipelined kernel: rounds staged by rank r
   unsigned long long pipe_b[kMaxBlocks][kMaxRanks];    // pipelined kernel: rounds reduced by rank r
 };
@@ -60,6 +61,7 @@ struct Params {
   void *keep[kMaxRanks];      // optional second destination = result-cache entry
   size_t bytes;               // payload bytes
   size_t stage_bytes;         // capacity of one stage (>= bytes rounded to 16)
+  size_t sym_offset;          // in-place kernels: offset of the symmetric user buffer inside every arena
   int root;                   // broadcast
   size_t slice_begin[kMaxRanks], slice_end[kMaxRanks];  // allgather (index 0 unless emulating)
   volatile int *abort_flag;   // host-mapped; non-zero = give up

@@ -30,6 +30,7 @@
 #include "coll_tma.cuh"
 #include "coll_nvls.cuh"
 #include "coll_pipe.cuh"
+#include "coll_inplace.cuh"
 #include "device_backend.h"
 #include "../host/engine_core.h"
 #include "rabit/internal/socket.h"

@@ -57,9 +57,10 @@ struct Config {
   std::string engine = "";                   // robust|mock|base|empty ; "" = library default
   std::string device = "auto";               // auto|on|off
   size_t device_arena = 0;                   // bytes of symmetric staging; 0 = grow on demand
+  size_t device_heap = 0;                    // bytes of symmetric heap for zero-copy buffers (RabitDeviceSymAlloc)
   size_t device_oneshot_max = 512 << 10;     // bytes: <= -> one-shot kernel
   size_t device_pipe_min = 8 << 20;          // bytes: >= -> pipelined (warp-specialised) two-shot
-  size_t device_nvls_min = 256 << 10;        // bytes: >= -> multimem kernel when available
+  size_t device_nvls_min = 64 << 10;         // bytes: >= -> multimem kernel when available
   int device_blocks = 0;                     // 0 = table default
   int device_timeout_ms = 20000;             // bounded spin before a peer is declared dead
   std::string device_algo = "auto";          // auto|oneshot|twoshot|tma|nvls
@@ -76,7 +77,7 @@ struct Config {
       "rabit_reduce_ring_mincount", "rabit_tree_reduce_minsize", "rabit_reduce_buffer",
       "rabit_engine", "rabit_device", "rabit_device_arena", "rabit_device_algo",
       "rabit_device_blocks", "rabit_device_timeout_ms", "rabit_device_force",
-      "rabit_device_oneshot_max", "rabit_device_nvls_min", "rabit_device_pipe_min", "rabit_device_cache",
+      "rabit_device_oneshot_max", "rabit_device_nvls_min", "rabit_device_pipe_min", "rabit_device_heap", "rabit_device_cache",
       "rabit_world_size", "rabit_slave_port"};
     return names;
   }
@@ -136,6 +137,7 @@ struct Config {
     else if (is("rabit_engine")) engine = val;
     else if (is("rabit_device")) device = val;
     else if (is("rabit_device_arena")) device_arena = ParseBytes(name, val);
+    else if (is("rabit_device_heap")) device_heap = ParseBytes(name, val);
     else if (is("rabit_device_oneshot_max")) device_oneshot_max = ParseBytes(name, val);
     else if (is("rabit_device_pipe_min")) device_pipe_min = ParseBytes(name, val);
     else if (is("rabit_device_nvls_min")) device_nvls_min = ParseBytes(name, val);
