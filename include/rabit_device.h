@@ -1,0 +1,68 @@
+/*!
+ * rabit-b200: C ABI of the device (sm_100a) side. Everything here is exported by lib/librabit*.so
+ * when the library was built with nvcc (python build.py); none of it exists in the reference,
+ * which has no GPU path at all.
+ *
+ * The fault-tolerant collectives need no extra API: RabitAllreduce / RabitBroadcast /
+ * RabitAllgather (rabit/c_api.h) recognise CUDA device pointers and run the fused kernels.
+ * This header adds (1) stream-ordered, non-fault-tolerant variants for training loops,
+ * (2) symmetric (zero-copy) buffers, (3) tuning hooks and (4) the single-GPU rank emulation
+ * used by tests, smoke() and the 1-GPU benchmark.
+ *
+ * dtype / op integers are the rabit::engine::mpi enums (see rabit/c_api.h).
+ */
+#ifndef RABIT_DEVICE_H_
+#define RABIT_DEVICE_H_
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- state ------------------------------------------------------------------------------ */
+/* 1 when this thread's engine has an attached device backend */
+int RabitDeviceActive(void);
+/* 1 when the NVLS multicast mapping is up (multimem kernels selectable) */
+int RabitDeviceHasMulticast(void);
+/* human readable one-liner (arena kind and size, NVLS on/off ...); returns the full length */
+int RabitDeviceDescribe(char *out, size_t max_len);
+/* number of kernels of this library launched so far by this process */
+unsigned long long RabitDeviceLaunchCount(void);
+
+/* ---- stream-ordered collectives (enqueue only; no consensus, no result cache) ---------- */
+/* CUDA stream used for all device work of this thread's engine (default: the legacy stream 0) */
+void RabitDeviceSetStream(void *cuda_stream);
+/* 0 on success, negative when there is no backend or the arguments are unusable */
+int RabitDeviceAllreduceAsync(void *dptr, size_t count, int dtype, int op);
+int RabitDeviceBroadcastAsync(void *dptr, size_t bytes, int root);
+int RabitDeviceAllgatherAsync(void *dptr, size_t total_bytes, size_t slice_begin, size_t slice_end);
+/* wait for everything enqueued: 0 ok, 1 consensus mismatch, 2 peer timeout, 3 peer lost */
+int RabitDeviceSynchronize(void);
+
+/* ---- symmetric buffers (zero-copy collectives) ------------------------------------------ */
+/* Carve nbytes out of the symmetric heap (sized with rabit_device_heap=<bytes> at init). Collective:
+ * same order and sizes on every rank. NULL when exhausted / no backend. Freed as a whole. */
+void *RabitDeviceSymAlloc(size_t nbytes);
+void RabitDeviceSymReset(void);
+
+/* ---- tuning ------------------------------------------------------------------------------- */
+/* algo: "auto", "oneshot", "twoshot", "tma", "nvls", "pipe", "nvlspipe", "staged" (NULL keeps it);
+ * blocks: grid cap, 0 = default; trace != 0: block 0 records %globaltimer at its phase boundaries */
+void RabitDeviceSetTuning(const char *algo, int blocks, int trace);
+void RabitDeviceGetTrace(unsigned long long *out6);
+
+/* ---- single-GPU emulation of an nranks-wide collective ----------------------------------- */
+/* kind 0 allreduce (size = elements), 1 broadcast (size = bytes), 2 allgather (size = total bytes);
+ * algo 1 one-shot, 2 two-shot, 3 two-shot/TMA, 5 pipelined; bufs[r]/keeps[r] device pointers per
+ * emulated rank; codes[r] consensus words (NULL = 0); status_out[r]: 0 ok, 1 mismatch, 2 timeout.
+ * Allocates its arenas with cudaMalloc on first use. Returns 0 or a negative API error. */
+int RabitEmuCollective(int kind, int algo, int nranks, void **bufs, void **keeps, size_t size, int dtype, int op,
+                       int root, const size_t *slice_begin, const size_t *slice_end, const unsigned *codes,
+                       int blocks, int timeout_ms, int *status_out);
+void RabitEmuReset(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif  /* RABIT_DEVICE_H_ */
