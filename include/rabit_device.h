@@ -62,6 +62,22 @@ int RabitEmuCollective(int kind, int algo, int nranks, void **bufs, void **keeps
                        int blocks, int timeout_ms, int *status_out);
 void RabitEmuReset(void);
 
+/* ---- allocation-free variant -------------------------------------------------------------- */
+/* No counterpart in the reference. The emulated two-shot allreduce for callers that must not trigger
+ * a GPU allocation: processes whose device memory is owned in full by another allocator (a
+ * framework's caching pool, a fixed tenant budget) or that forbid driver allocations after start-up.
+ * All scratch (flags, staging, status) is a static __device__ array inside the library: about 6 MiB
+ * that every GPU loading the library holds until exit. Limits: at most 8 ranks and 256 KiB of
+ * payload per rank; anything larger returns -3 with a message on stderr. The call clears the part
+ * of the scratch that must start at zero, on `cuda_stream`, and then launches there; all calls share
+ * the scratch, so calls that overlap on the GPU race. The first call on a device looks up the
+ * array's address and must be made outside stream capture. bufs[r] are caller-owned device
+ * buffers reduced in place. With status_out != NULL the call waits for the stream and reports one
+ * status per rank (0 ok, 1 mismatch, 2 timeout). Returns 0, or -1 bad arguments, -2 unsupported
+ * dtype/op, -3 too large, -4 CUDA error. */
+int RabitEmuAllreduceNoAlloc(int nranks, void **bufs, size_t count, int dtype, int op, void *cuda_stream,
+                             int *status_out);
+
 #ifdef __cplusplus
 }
 #endif
