@@ -158,14 +158,10 @@ class Tracker(object):
             want.add(prv)
         if nxt not in (-1, rank):
             want.add(nxt)
-        c.send_int(rank)
-        c.send_int(parent[rank])
-        c.send_int(n)
-        c.send_int(len(tree[rank]))
-        for r in tree[rank]:
-            c.send_int(r)
-        c.send_int(prv if prv != rank else -1)
-        c.send_int(nxt if nxt != rank else -1)
+        # one segment for the whole assignment (rank, parent, world, tree neighbours, ring neighbours)
+        msg = [rank, parent[rank], n, len(tree[rank])] + list(tree[rank])
+        msg += [prv if prv != rank else -1, nxt if nxt != rank else -1]
+        c.sock.sendall(struct.pack("@%di" % len(msg), *msg))
         dialled = []
         while True:
             ngood = c.recv_int()
@@ -177,12 +173,11 @@ class Tracker(object):
                     wait_conn.pop(r, None)
             bad = want - good
             dial = [r for r in sorted(bad) if r in wait_conn]
-            c.send_int(len(dial))
-            c.send_int(len(bad) - len(dial))
+            out = struct.pack("@ii", len(dial), len(bad) - len(dial))
             for r in dial:
-                c.send_str(wait_conn[r].host)
-                c.send_int(wait_conn[r].port)
-                c.send_int(r)
+                h = wait_conn[r].host.encode()
+                out += struct.pack("@i", len(h)) + h + struct.pack("@ii", wait_conn[r].port, r)
+            c.sock.sendall(out)
             dialled = dial
             if c.recv_int() != 0:
                 continue
@@ -206,6 +201,9 @@ class Tracker(object):
         todo = list(range(n))  # ranks not handed out yet
         while len(shutdown) < n:
             fd, addr = self.sock.accept()
+            # the protocol is a chain of tiny writes followed by a read: without TCP_NODELAY every such
+            # exchange stalls ~40 ms in Nagle + delayed ACK, which dominated recover-after-kill time
+            fd.setsockopt(socket.IPPROTO_TCP, socket.TCP_NODELAY, 1)
             c = _Conn(fd, addr)
             try:
                 c.handshake()

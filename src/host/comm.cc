@@ -94,6 +94,7 @@ utils::TCPSocket HostComm::DialTracker() {
   utils::SockAddr addr(cfg.tracker_uri.c_str(), cfg.tracker_port);
   for (int attempt = 1;; ++attempt) {
     t.Create();
+    t.SetNoDelay(true);  // the handshake is many tiny writes followed by reads: avoid Nagle stalls
     if (t.Connect(addr)) break;
     t.Close();
     utils::Check(attempt < std::max(cfg.connect_retry, 1), "cannot reach tracker %s:%d after %d attempts",
