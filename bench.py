@@ -270,6 +270,10 @@ def run_ours(args):
             t = timed(lambda: rt.broadcast_async_(v, 0), it, 3)
             row["broadcast_us"] = t * 1e3
             row["broadcast_busbw_GBps"] = sz / (t * 1e-3) / 1e9
+            if n > 1:
+                t = timed(lambda: rt.broadcast_async_(vs, 0), it, 3)
+                row["broadcast_sym_us"] = t * 1e3
+                row["broadcast_sym_busbw_GBps"] = sz / (t * 1e-3) / 1e9
             if have_nccl:
                 t = timed_nccl(dist, torch, v, it, 3, rabit, np)
                 row["nccl_allreduce_us"] = t * 1e3
@@ -278,6 +282,26 @@ def run_ours(args):
                 row["nccl_broadcast_us"] = t * 1e3
                 row["nccl_broadcast_busbw_GBps"] = sz / (t * 1e-3) / 1e9
             sweep.append(row)
+        # BASELINE config 3: XGBoost-style gradient histogram, 1000 features x 256 bins x {double grad, double hess}
+        # = 4.096 MB, reduced with the pair-sum reducer = float64 Sum over 2x the elements
+        hcount = 1000 * 256 * 2
+        hs = rt.symmetric_empty(hcount, torch.float64) if n > 1 else torch.zeros(hcount, dtype=torch.float64, device=dev)
+        hp = torch.zeros(hcount, dtype=torch.float64, device=dev)
+        hist = {"bytes": hcount * 8}
+        hist["sym_us"] = timed(lambda: rt.allreduce_async_(hs), 50, 5) * 1e3
+        hist["staged_us"] = timed(lambda: rt.allreduce_async_(hp), 50, 5) * 1e3
+        if have_nccl:
+            hist["nccl_us"] = timed_nccl(dist, torch, hp, 50, 5, rabit, np) * 1e3
+        for _ in range(3):
+            rabit.allreduce(hp, rabit.SUM)          # robust public API (consensus + cache copy fused)
+        rabit.checkpoint(0)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(50):
+            rabit.allreduce(hp, rabit.SUM)
+        torch.cuda.synchronize()
+        hist["robust_api_us"] = max_over_ranks(rabit, np, (time.perf_counter() - t0) * 1e6 / 50)
+        rabit.checkpoint(0)
         if have_nccl:
             dist.destroy_process_group()
 
@@ -312,6 +336,7 @@ def run_ours(args):
             out["nccl"] = {"ms_per_step": nccl_ms, "busbw_GBps": S / (nccl_ms * 1e-3) / 1e9 * (2.0 * (n - 1) / n)}
         if sweep:
             out["sweep"] = sweep
+            out["histogram_pair_sum_f64_4MB"] = hist
         print(json.dumps(out), flush=True)
     if tracker is not None:
         tracker.join(10)

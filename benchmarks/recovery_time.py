@@ -53,7 +53,9 @@ def main():
         env = {"PYTHONPATH": ROOT}
         impls = {"ours (device buffers, %d GPUs)" % args.gpus:
                  ([sys.executable, os.path.join(ROOT, "tests", "gpu_worker.py"), "200000"],
-                  {"env": env, "per_rank_gpu": True})}
+                  {"env": env, "per_rank_gpu": True}),
+                 "ours (device buffers, native C++ worker, %d GPUs)" % args.gpus:
+                 ([os.path.join(ROOT, "build", "bin", "device_recover_cuda"), "200000"], {"per_rank_gpu": True})}
         args.world = args.gpus
     common = ["rabit_bootstrap_cache=1", "rabit_enable_tcp_no_delay=true"]
     rows = []

@@ -134,9 +134,17 @@ def build(cuda=True, verbose=False, programs=True):
             # programs that use mock= link the mock library, like the reference's test/Makefile
             lib = "rabit_mock"
             exe = os.path.join(bin_dir, name)
+            extra = []
+            if name.endswith("_cuda"):
+                # programs that own device buffers: CUDA runtime API from plain C++
+                if not cuda:
+                    continue
+                cuda_home = os.path.dirname(os.path.dirname(nvcc))
+                extra = ["-I" + os.path.join(cuda_home, "include"), "-L" + os.path.join(cuda_home, "lib64"),
+                         "-lcudart_static", "-ldl", "-lrt"]
             if newer([src] + hdrs + [os.path.join(ROOT, "lib", "lib%s.so" % lib)], exe):
                 pjobs.append(["g++"] + CXXFLAGS + [src, "-o", exe, "-L" + os.path.join(ROOT, "lib"),
-                                                   "-l" + lib, "-Wl,-rpath," + os.path.join("$ORIGIN", "..", "..", "lib")])
+                                                   "-l" + lib, "-Wl,-rpath," + os.path.join("$ORIGIN", "..", "..", "lib")] + extra)
         with concurrent.futures.ThreadPoolExecutor(max_workers=os.cpu_count() or 4) as ex:
             for f in [ex.submit(run, c, not verbose) for c in pjobs]:
                 f.result()

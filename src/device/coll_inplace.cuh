@@ -158,6 +158,153 @@ __global__ void __launch_bounds__(512) NvlsInPlace(Params p) {
   Stamp(p, 5);
 }
 
+/*!
+ * \brief zero-copy broadcast: the root stores its symmetric buffer through the multicast mapping, the
+ *  switch writes it into every rank's copy of the buffer; one barrier tells everybody it is complete.
+ */
+__global__ void __launch_bounds__(512) NvlsBroadcastInPlace(Params p) {
+  __shared__ int s_verdict;
+  const int me = p.rank;
+  char *keep = static_cast<char *>(p.keep[0]);
+  const size_t nvec = (p.bytes + kVec - 1) / kVec;
+  const size_t tile_vecs = static_cast<size_t>(blockDim.x) * kNvlsUnroll;
+  const size_t ntiles = (nvec + tile_vecs - 1) / tile_vecs;
+  // nobody may still be using the previous contents of its buffer when the root starts overwriting it
+  int verdict = FlagBarrier(p, me, EntryRow{p.epoch & 1u}, p.epoch + 1, p.code[0], true, &s_verdict);
+  if (verdict != kStOk) { Report(p, me, verdict); return; }
+  if (me == p.root) {
+    const char *src = SymOf(p, me);
+    char *mc = p.mc_arena + p.sym_offset;
+    for (size_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+      const size_t v0 = tile * tile_vecs + threadIdx.x;
+      uint4 r[kNvlsUnroll];
+#pragma unroll
+      for (int u = 0; u < kNvlsUnroll; ++u) {
+        const size_t v = v0 + static_cast<size_t>(u) * blockDim.x;
+        if (v < nvec) r[u] = LoadVec(src + v * kVec);
+      }
+#pragma unroll
+      for (int u = 0; u < kNvlsUnroll; ++u) {
+        const size_t v = v0 + static_cast<size_t>(u) * blockDim.x;
+        if (v < nvec) {
+          MultimemStore(mc + v * kVec, r[u]);
+          if (keep != nullptr) StoreVec(keep + v * kVec, r[u]);
+        }
+      }
+    }
+  }
+  verdict = FlagBarrier(p, me, MidRow{}, p.epoch + 1, 0u, false, &s_verdict);
+  if (verdict != kStOk) { Report(p, me, verdict); return; }
+  if (me != p.root && keep != nullptr) {
+    const char *src = SymOf(p, me);
+    for (size_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+      const size_t v0 = tile * tile_vecs + threadIdx.x;
+#pragma unroll
+      for (int u = 0; u < kNvlsUnroll; ++u) {
+        const size_t v = v0 + static_cast<size_t>(u) * blockDim.x;
+        if (v < nvec) StoreVec(keep + v * kVec, LoadVec(src + v * kVec));
+      }
+    }
+  }
+}
+
+/*!
+ * \brief staged broadcast through the switch, chunk-pipelined: the root streams its (ordinary) user
+ *  buffer into everybody's stage with multimem.st and publishes a per-block round counter every
+ *  kBcastRoundTiles tiles; the other ranks copy finished rounds out of their stage while later rounds
+ *  are still in flight. Needs 16-byte aligned buffers and a size that is a multiple of 16.
+ */
+constexpr int kBcastRoundTiles = 4;
+
+__global__ void __launch_bounds__(512) NvlsBroadcastPipe(Params p, unsigned long long round_base) {
+  __shared__ int s_verdict;
+  __shared__ int s_abort;
+  const int me = p.rank;
+  char *user = static_cast<char *>(p.user[0]);
+  char *keep = static_cast<char *>(p.keep[0]);
+  const int b = blockIdx.x, G = gridDim.x, n = p.world;
+  const size_t nvec = p.bytes / kVec;
+  const size_t tile_vecs = static_cast<size_t>(blockDim.x) * kUnroll;
+  const size_t ntiles = (nvec + tile_vecs - 1) / tile_vecs;
+  const size_t chan_tiles = ntiles > static_cast<size_t>(b) ? (ntiles - b + G - 1) / G : 0;
+  const size_t rounds = (chan_tiles + kBcastRoundTiles - 1) / kBcastRoundTiles;
+  if (threadIdx.x == 0) s_abort = 0;
+  // stage[parity] of every rank is free once everybody has entered this op (see coll_common.cuh)
+  int verdict = FlagBarrier(p, me, EntryRow{p.epoch & 1u}, p.epoch + 1, p.code[0], true, &s_verdict);
+  if (verdict != kStOk) { Report(p, me, verdict); return; }
+  if (me == p.root) {
+    char *mc = McStage(p);
+    for (size_t j = 0; j < rounds; ++j) {
+      for (int i = 0; i < kBcastRoundTiles; ++i) {
+        const size_t k = j * kBcastRoundTiles + i;
+        if (k >= chan_tiles) break;
+        const size_t v0 = (b + k * G) * tile_vecs + threadIdx.x;
+        uint4 r[kUnroll];
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+          const size_t v = v0 + static_cast<size_t>(u) * blockDim.x;
+          if (v < nvec) r[u] = LoadVec(user + v * kVec);
+        }
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+          const size_t v = v0 + static_cast<size_t>(u) * blockDim.x;
+          if (v < nvec) {
+            MultimemStore(mc + v * kVec, r[u]);
+            if (keep != nullptr) StoreVec(keep + v * kVec, r[u]);
+          }
+        }
+      }
+      __syncthreads();
+      if (threadIdx.x < n) StoreReleaseSys(&CtrlOf(p, threadIdx.x)->pipe_a[b][me], round_base + j + 1);
+    }
+  } else {
+    const char *src = StageOf(p, me);
+    const unsigned long long *slot = &CtrlOf(p, me)->pipe_a[b][p.root];
+    for (size_t j = 0; j < rounds; ++j) {
+      if (threadIdx.x == 0) {
+        const unsigned long long deadline = GlobalTimer() + p.timeout_ns;
+        unsigned int spins = 0;
+        while (LoadAcquireSys(slot) < round_base + j + 1) {
+          if ((++spins & 0x3ff) == 0) {
+            if (*p.abort_flag != 0) { s_abort = kStAborted; break; }
+            if (GlobalTimer() > deadline) { s_abort = kStTimeout; break; }
+          }
+        }
+      }
+      __syncthreads();
+      if (s_abort != 0) break;
+      for (int i = 0; i < kBcastRoundTiles; ++i) {
+        const size_t k = j * kBcastRoundTiles + i;
+        if (k >= chan_tiles) break;
+        const size_t v0 = (b + k * G) * tile_vecs + threadIdx.x;
+        uint4 r[kUnroll];
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+          const size_t v = v0 + static_cast<size_t>(u) * blockDim.x;
+          if (v < nvec) r[u] = LoadVec(src + v * kVec);
+        }
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+          const size_t v = v0 + static_cast<size_t>(u) * blockDim.x;
+          if (v < nvec) {
+            StoreVec(user + v * kVec, r[u]);
+            if (keep != nullptr) StoreVec(keep + v * kVec, r[u]);
+          }
+        }
+      }
+    }
+    if (s_abort != 0) Report(p, me, s_abort);
+  }
+}
+
+/*! \brief rounds NvlsBroadcastPipe consumes (same on every rank) */
+inline unsigned long long BcastRounds(size_t bytes, int grid) {
+  const size_t tile = 512 * kUnroll * kVec;
+  const size_t ntiles = (bytes + tile - 1) / tile;
+  const size_t per_chan = (ntiles + grid - 1) / grid;
+  return (per_chan + kBcastRoundTiles - 1) / kBcastRoundTiles;
+}
+
 }  // namespace device
 }  // namespace rabit
 #endif  // RABIT_SRC_DEVICE_COLL_INPLACE_CUH_

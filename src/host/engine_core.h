@@ -238,6 +238,13 @@ class RobustEngine : public BaseEngine {
   Status CompleteLocal(int which);
   /*! \brief gather `nwords` 64-bit words from every rank into a world x nwords table */
   Status GatherTable(const uint64_t *mine, int nwords, std::vector<uint64_t> *table);
+  /*!
+   * \brief large recovery payloads go over NVLink instead of the TCP ring when every rank has a device
+   *  backend: the lowest-ranked holder uploads the blob, ONE broadcast kernel (multicast store where the
+   *  switch supports it) fans it out, requesters download it. Returns false if that path is not usable.
+   */
+  bool DeviceDeliver(const std::vector<char> &has, const std::vector<char> &need, const void *src_host,
+                     const void *src_dev, void *dst_host, size_t size, Status *st);
   /*! \brief move one blob from its holders to the ranks that need it, along the ring */
   Status RingDeliver(const std::vector<char> &has, const std::vector<char> &need, void *buf, size_t size);
 

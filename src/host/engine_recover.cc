@@ -8,6 +8,7 @@
  * (1328-1511). The reference negotiates routes with two tree message-passing rounds
  * (TryDecideRouting 798-845); here the table makes the plan explicit instead.
  */
+#include "../device/device_backend.h"
 #include "engine_core.h"
 
 namespace rabit {
@@ -38,11 +39,41 @@ Status RobustEngine::ServeResult(void *buf, size_t size, uint32_t seq, bool requ
                  "in current VersionNumber (rank %d expects %lu bytes, cached %lu)", r,
                  static_cast<unsigned long>(tab[r * 3 + 2]), static_cast<unsigned long>(held_size));  // NOLINT(*)
   }
+  {
+    Status dst = Status::kOk;
+    const void *src_dev = held != nullptr ? held->dev : nullptr;
+    const void *src_host = (held != nullptr && held->dev == nullptr) ? held->host.data() : nullptr;
+    if (DeviceDeliver(has, need, src_host, src_dev, requester ? buf : nullptr, held_size, &dst)) return dst;
+  }
   // only a holder whose successor actually pulls pays for a device->host copy of the entry
   void *p = requester ? buf : nullptr;
   if (held != nullptr && !has[(comm_.rank + 1) % n]) p = results_.HostView(held);
   if (held != nullptr && p == nullptr) return Status::kOk;
   return RingDeliver(has, need, p, held_size);
+}
+
+bool RobustEngine::DeviceDeliver(const std::vector<char> &has, const std::vector<char> &need,
+                                 const void *src_host, const void *src_dev, void *dst_host, size_t size,
+                                 Status *st) {
+  const size_t kMinBytes = 4u << 20;  // below this the TCP ring is as fast and needs no GPU round trip
+  if (device_ == nullptr || !device_->attached() || size < kMinBytes) return false;
+  int root = -1;
+  for (int r = 0; r < comm_.world && root < 0; ++r) if (has[r]) root = r;
+  if (root < 0) return false;
+  // every rank takes part in the kernel, whether it needs the bytes or not
+  void *d = device_->Alloc(size);
+  if (comm_.rank == root) {
+    if (src_dev != nullptr) device_->CopyD2D(d, src_dev, size);
+    else device_->CopyH2D(d, src_host, size);
+  }
+  *st = device_->Broadcast(d, size, root, 0x7ffffff0u, nullptr);
+  if (Ok(*st) && need[comm_.rank] && dst_host != nullptr) device_->CopyD2H(dst_host, d, size);
+  device_->Free(d);
+  if (comm_.cfg.debug) {
+    utils::HandleLogInfo("[%d] recovery payload of %lu bytes moved over NVLink from rank %d (%s)\n", comm_.rank,
+                         static_cast<unsigned long>(size), root, StatusName(*st));  // NOLINT(*)
+  }
+  return true;
 }
 
 void RobustEngine::MaterializeLazy() {
@@ -76,6 +107,11 @@ Status RobustEngine::ServeLoad(bool requester) {
   utils::Check(any, "[%d] LoadCheckPoint: no surviving rank holds the global checkpoint", comm_.rank);
   if (requester) global_blob_.resize(size);
   if (size == 0) return Status::kOk;  // nothing committed yet: version 0
+  {
+    Status dst = Status::kOk;
+    if (DeviceDeliver(has, need, holder ? global_blob_.data() : nullptr, nullptr,
+                      requester ? &global_blob_[0] : nullptr, size, &dst)) return dst;
+  }
   void *p = (requester || holder) ? &global_blob_[0] : nullptr;
   return RingDeliver(has, need, p, size);
 }

@@ -48,3 +48,22 @@ def test_device_recovery_after_kills(world):
     assert res.restarts == 2
     for i, o in res.outputs.items():
         assert "iter 2 checkpointed" in o
+
+
+def test_device_recovery_large_payload_over_nvlink(world):
+    """12 MB results and checkpoint: recovery payloads of that size travel as ONE broadcast kernel over
+    NVLink (RobustEngine::DeviceDeliver) instead of the TCP ring"""
+    res = _run(["3000000", "iters=2", "mock=1,1,1,0", "rabit_debug=1", "rabit_timeout=1", "rabit_timeout_sec=120"],
+               world, timeout=600)
+    assert res.ok, {i: o[-2500:] for i, o in res.outputs.items()}
+    assert res.restarts == 1
+    assert any("moved over NVLink" in o for o in res.outputs.values())
+
+
+def test_native_cpp_device_workload_with_kills(world):
+    """the C++ public API (rabit::Allreduce / Broadcast on device pointers) incl. recovery"""
+    from conftest import bin_path
+    res = run_job([bin_path("device_recover_cuda"), "100000", "mock=0,0,1,0", "mock=1,1,2,0"], world, timeout=300,
+                  per_rank_gpu=True)
+    assert res.ok, {i: o[-2000:] for i, o in res.outputs.items()}
+    assert res.restarts == 2
