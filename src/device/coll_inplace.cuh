@@ -297,6 +297,163 @@ __global__ void __launch_bounds__(512) NvlsBroadcastPipe(Params p, unsigned long
   }
 }
 
+/*!
+ * \brief broadcast as scatter + multicast allgather. A single GPU streaming the whole buffer through
+ *  multimem.st reaches only ~390-540 GB/s (measured, 8 and 2 B200); eight GPUs multicasting an eighth
+ *  each saturate the fabric. So the root P2P-stores tile k of every channel into the buffer of rank
+ *  k % world (its own share goes straight through the multicast mapping), and every rank re-emits the
+ *  tiles it received with multimem.st. Rounds of `world` tiles are pipelined with per-block counters:
+ *  A[root] "round scattered", B[i] "rank i has multicast its tile of the round".
+ *  inplace != 0: source and destination are the symmetric user buffer (no copy-out at all);
+ *  otherwise the data lands in the stage and each rank copies finished rounds out to its user buffer.
+ *  direct != 0 (used for 2 ranks, where re-emitting would send every byte across twice): the root
+ *  simply P2P-stores every tile into every peer and the peers only wait for A.
+ */
+__global__ void __launch_bounds__(512) BroadcastScatterMc(Params p, unsigned long long round_base, int inplace,
+                                                          int direct) {
+  __shared__ int s_verdict;
+  __shared__ int s_abort;
+  const int me = p.rank, n = p.world, root = p.root;
+  const int b = blockIdx.x, G = gridDim.x;
+  char *user = static_cast<char *>(p.user[0]);
+  char *keep = static_cast<char *>(p.keep[0]);
+  const size_t nvec = p.bytes / kVec;
+  const size_t tile_vecs = static_cast<size_t>(blockDim.x) * kUnroll;
+  const size_t ntiles = (nvec + tile_vecs - 1) / tile_vecs;
+  const size_t chan_tiles = ntiles > static_cast<size_t>(b) ? (ntiles - b + G - 1) / G : 0;
+  const size_t rounds = (chan_tiles + n - 1) / n;
+  if (threadIdx.x == 0) s_abort = 0;
+  int verdict = FlagBarrier(p, me, EntryRow{p.epoch & 1u}, p.epoch + 1, p.code[0], true, &s_verdict);
+  if (verdict != kStOk) { Report(p, me, verdict); return; }
+  char *my_dst = inplace ? SymOf(p, me) : StageOf(p, me);
+  char *mc_dst = inplace ? p.mc_arena + p.sym_offset : McStage(p);
+  Control *my_ctrl = CtrlOf(p, me);
+  // one thread waits for a counter, the block follows; returns false when the op must be abandoned
+  auto wait_for = [&](const unsigned long long *slot, unsigned long long target) -> bool {
+    if (threadIdx.x == 0) {
+      const unsigned long long deadline = GlobalTimer() + p.timeout_ns;
+      unsigned int spins = 0;
+      while (LoadAcquireSys(slot) < target) {
+        if ((++spins & 0x3ff) == 0) {
+          if (*p.abort_flag != 0) { s_abort = kStAborted; break; }
+          if (GlobalTimer() > deadline) { s_abort = kStTimeout; break; }
+        }
+      }
+    }
+    __syncthreads();
+    return s_abort == 0;
+  };
+  auto copy_out = [&](size_t j) {  // stage -> user (+keep) for every tile of round j
+    for (int i = 0; i < n; ++i) {
+      const size_t k = j * n + i;
+      if (k >= chan_tiles) break;
+      const size_t v0 = (b + k * G) * tile_vecs + threadIdx.x;
+      uint4 r[kUnroll];
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        const size_t v = v0 + static_cast<size_t>(u) * blockDim.x;
+        if (v < nvec) r[u] = LoadVec(my_dst + v * kVec);
+      }
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        const size_t v = v0 + static_cast<size_t>(u) * blockDim.x;
+        if (v < nvec) {
+          if (!inplace) StoreVec(user + v * kVec, r[u]);
+          if (keep != nullptr) StoreVec(keep + v * kVec, r[u]);
+        }
+      }
+    }
+  };
+  if (me == root) {
+    const char *src = inplace ? my_dst : user;
+    for (size_t j = 0; j < rounds; ++j) {
+      for (int i = 0; i < n; ++i) {
+        const size_t k = j * n + i;
+        if (k >= chan_tiles) break;
+        const size_t v0 = (b + k * G) * tile_vecs + threadIdx.x;
+        char *peer = inplace ? SymOf(p, i) : StageOf(p, i);
+        uint4 r[kUnroll];
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+          const size_t v = v0 + static_cast<size_t>(u) * blockDim.x;
+          if (v < nvec) r[u] = LoadVec(src + v * kVec);
+        }
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+          const size_t v = v0 + static_cast<size_t>(u) * blockDim.x;
+          if (v < nvec) {
+            if (direct) {
+              for (int q = 0; q < n; ++q) {
+                if (q != root) StoreVec((inplace ? SymOf(p, q) : StageOf(p, q)) + v * kVec, r[u]);
+              }
+            } else if (i == root) {
+              MultimemStore(mc_dst + v * kVec, r[u]);
+            } else {
+              StoreVec(peer + v * kVec, r[u]);
+            }
+            if (keep != nullptr) StoreVec(keep + v * kVec, r[u]);
+          }
+        }
+      }
+      __syncthreads();
+      if (threadIdx.x < n) StoreReleaseSys(&CtrlOf(p, threadIdx.x)->pipe_a[b][me], round_base + j + 1);
+    }
+    if (inplace && !direct) {
+      // peers still multicast old tiles into OUR buffer: do not return (and let the caller refill it) before they are done
+      for (int i = 0; i < n; ++i) {
+        if (i != root && !wait_for(&my_ctrl->pipe_b[b][i], round_base + rounds)) break;
+      }
+    }
+  } else {
+    for (size_t j = 0; j <= rounds; ++j) {
+      if (j < rounds) {
+        if (!wait_for(&my_ctrl->pipe_a[b][root], round_base + j + 1)) break;
+        if (direct) {
+          if (!inplace || keep != nullptr) copy_out(j);
+          continue;
+        }
+        const size_t k = j * n + me;
+        if (k < chan_tiles) {
+          const size_t v0 = (b + k * G) * tile_vecs + threadIdx.x;
+          uint4 r[kUnroll];
+#pragma unroll
+          for (int u = 0; u < kUnroll; ++u) {
+            const size_t v = v0 + static_cast<size_t>(u) * blockDim.x;
+            if (v < nvec) r[u] = LoadVec(my_dst + v * kVec);
+          }
+#pragma unroll
+          for (int u = 0; u < kUnroll; ++u) {
+            const size_t v = v0 + static_cast<size_t>(u) * blockDim.x;
+            if (v < nvec) MultimemStore(mc_dst + v * kVec, r[u]);
+          }
+        }
+        __syncthreads();
+        if (threadIdx.x < n) StoreReleaseSys(&CtrlOf(p, threadIdx.x)->pipe_b[b][me], round_base + j + 1);
+      }
+      if (direct) continue;
+      if (j > 0) {
+        // round j-1: every owner except the root announces its tile through B; the root's own tile and the
+        // scatter itself are covered by A (already awaited above for round j-1)
+        bool ok = true;
+        for (int i = 0; i < n && ok; ++i) {
+          if (i != root && i != me) ok = wait_for(&my_ctrl->pipe_b[b][i], round_base + j);
+        }
+        if (!ok) break;
+        if (!inplace || keep != nullptr) copy_out(j - 1);
+      }
+    }
+  }
+  if (s_abort != 0) Report(p, me, s_abort);
+}
+
+/*! \brief rounds BroadcastScatterMc consumes */
+inline unsigned long long ScatterRounds(size_t bytes, int grid, int world) {
+  const size_t tile = 512 * kUnroll * kVec;
+  const size_t ntiles = (bytes + tile - 1) / tile;
+  const size_t per_chan = (ntiles + grid - 1) / grid;
+  return (per_chan + world - 1) / world;
+}
+
 /*! \brief rounds NvlsBroadcastPipe consumes (same on every rank) */
 inline unsigned long long BcastRounds(size_t bytes, int grid) {
   const size_t tile = 512 * kUnroll * kVec;

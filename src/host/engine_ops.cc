@@ -231,7 +231,11 @@ int RobustEngine::LoadCheckPoint(Serializable *global_model, Serializable *local
 }
 
 void RobustEngine::Commit(const Serializable *global_model, const Serializable *local_model, bool lazy) {
-  if (comm_.world <= 1) { ++version_number_; return; }
+  if (comm_.world <= 1) {
+    // nothing to replicate; with rabit_device_force the result cache still fills up, so empty it
+    ++version_number_; results_.Clear(); seq_ = 0;
+    return;
+  }
   checkpoint_loaded_ = true;  // a commit also ends the bootstrap phase
   const double t0 = utils::GetTime();
   LocalModelCheck(local_model != nullptr);

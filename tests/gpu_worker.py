@@ -33,6 +33,10 @@ def main():
     rabit.init(sys.argv, lib="mock")
     me, world = rabit.get_rank(), rabit.get_world_size()
     assert rt.device_active(), rt.describe()
+    sym = None
+    if any(a.startswith("rabit_device_heap=") for a in sys.argv):
+        # collective allocation, same order on every rank (also after a restart)
+        sym = (rt.symmetric_empty(1 << 20, torch.float32), rt.symmetric_empty(2 << 20, torch.uint8))
     version, model = rabit.load_checkpoint()
     if version == 0:
         model = np.ones(n, dtype=np.float32)
@@ -72,6 +76,31 @@ def main():
         rt.allgather_(g, me * per, per)
         want = torch.arange(world, device=dev, dtype=torch.int32).repeat_interleave(per) * 1000 + it
         assert torch.equal(g, want), "[%d] allgather mismatch iter %d" % (me, it)
+        # large (>= 1 MiB) broadcast: scatter + multicast-allgather kernel where NVLS is up
+        big = 3 * (1 << 20) + 4096
+        bb = torch.zeros(big, dtype=torch.uint8, device=dev)
+        btruth = ((torch.arange(big, device=dev) * 13 + root + it) % 253).to(torch.uint8)
+        if me == root:
+            bb.copy_(btruth)
+        rt.broadcast_(bb, root)
+        assert torch.equal(bb, btruth), "[%d] large broadcast mismatch iter %d" % (me, it)
+        if sym is not None:
+            # zero-copy path: the same collectives on buffers from the symmetric heap
+            sx, sb = sym
+            sx.copy_(contribution(sx.numel(), me, it, 101, dev))
+            rabit.allreduce(sx, rabit.SUM)
+            want = torch.stack([contribution(sx.numel(), r, it, 101, dev) for r in range(world)]).sum(0)
+            assert torch.equal(sx, want), "[%d] symmetric allreduce mismatch iter %d" % (me, it)
+            sx.copy_(contribution(sx.numel(), me, it, 103, dev))
+            rabit.allreduce(sx, rabit.MAX)
+            want = torch.stack([contribution(sx.numel(), r, it, 103, dev) for r in range(world)]).max(0).values
+            assert torch.equal(sx, want), "[%d] symmetric max mismatch iter %d" % (me, it)
+            if me == root:
+                sb.copy_(btruth[:sb.numel()])
+            else:
+                sb.zero_()
+            rt.broadcast_(sb, root)
+            assert torch.equal(sb, btruth[:sb.numel()]), "[%d] symmetric broadcast mismatch iter %d" % (me, it)
         model = y % 1000.0
         rabit.checkpoint(model.cpu().numpy())
         print("[%d] iter %d checkpointed (version %d)" % (me, it, rabit.version_number()), flush=True)

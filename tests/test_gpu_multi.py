@@ -67,3 +67,10 @@ def test_native_cpp_device_workload_with_kills(world):
                   per_rank_gpu=True)
     assert res.ok, {i: o[-2000:] for i, o in res.outputs.items()}
     assert res.restarts == 2
+
+
+def test_device_symmetric_zero_copy_buffers(world):
+    """allreduce / broadcast on RabitDeviceSymAlloc buffers (in-place kernels), also across a kill"""
+    res = _run(["100000", "rabit_device_heap=64M", "mock=1,1,3,0"], world, timeout=600)
+    assert res.ok, {i: o[-2500:] for i, o in res.outputs.items()}
+    assert res.restarts == 1
