@@ -40,6 +40,7 @@ def build(force=False):
     srcs = [os.path.join(copy, "src", f) for f in ("allreduce_base.cc", "allreduce_robust.cc", "engine.cc", "c_api.cc")]
     for name, main in (("ref_speed", os.path.join(HERE, "ref_speed.cc")),
                        ("ref_model_recover", os.path.join(copy, "test", "model_recover.cc")),
+                       ("ref_speed_test", os.path.join(copy, "test", "speed_test.cc")),
                        ("ref_basic", os.path.join(copy, "guide", "basic.cc"))):
         # the reference's test programs are linked with its mock engine (test/Makefile:67)
         eng = [os.path.join(copy, "src", "engine_mock.cc" if name == "ref_model_recover" else "engine.cc")]

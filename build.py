@@ -75,6 +75,11 @@ def build(cuda=True, verbose=False, programs=True):
     if cuda and nvcc is None:
         raise RuntimeError("nvcc not found; pass --no-cuda for a host-only build")
     obj_dir = os.path.join(ROOT, "build", "obj_cuda" if cuda else "obj_host")
+    # the two flavours share lib/: remember which one is there so that switching always relinks
+    flavour = os.path.join(ROOT, "lib", ".flavour")
+    want = "cuda" if cuda else "host"
+    have = open(flavour).read().strip() if os.path.exists(flavour) else ""
+    relink = have != want
     os.makedirs(obj_dir, exist_ok=True)
     os.makedirs(os.path.join(ROOT, "lib"), exist_ok=True)
     hdrs = headers()
@@ -118,13 +123,15 @@ def build(cuda=True, verbose=False, programs=True):
     link_tail = ["-pthread", "-ldl", "-lrt"]
     for lib, eo in engine_objs.items():
         target = os.path.join(ROOT, "lib", lib)
-        if newer(objs + [eo], target):
+        if relink or newer(objs + [eo], target):
             if cuda:
                 run([nvcc] + NVCC_ARCH + ["-shared", "-o", target] + objs + [eo] +
                     ["-cudart", "static", "-Xcompiler", "-pthread"] + ["-ldl", "-lrt"], not verbose)
             else:
                 run(["g++", "-shared", "-o", target] + objs + [eo] + link_tail, not verbose)
 
+    with open(flavour, "w") as fo:
+        fo.write(want)
     if programs:
         bin_dir = os.path.join(ROOT, "build", "bin")
         os.makedirs(bin_dir, exist_ok=True)

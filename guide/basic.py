@@ -1,0 +1,23 @@
+#!/usr/bin/env python
+"""rabit-b200 guide: allreduce from python (cf. reference guide/basic.py).
+   python -m rabit_b200.parallel.launcher -n 4 python guide/basic.py"""
+import os
+import sys
+
+import numpy as np
+
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), ".."))
+from rabit_b200 import rabit  # noqa: E402
+
+rabit.init()
+n = 3
+rank = rabit.get_rank()
+a = np.zeros(n)
+for i in range(n):
+    a[i] = rank + i
+print("@node[%d] before-allreduce: a=%s" % (rank, str(a)))
+a = rabit.allreduce(a, rabit.MAX)
+print("@node[%d] after-allreduce-max: a=%s" % (rank, str(a)))
+a = rabit.allreduce(a, rabit.SUM)
+print("@node[%d] after-allreduce-sum: a=%s" % (rank, str(a)))
+rabit.finalize()

@@ -1,0 +1,1 @@
+"""Workloads built on the collectives: gradient-histogram aggregation and torch checkpoint helpers."""

@@ -1,0 +1,1 @@
+"""Device ops: `emulate` drives the real kernels with N virtual ranks on one GPU."""

@@ -1,0 +1,1 @@
+"""Rendezvous tracker and local launcher (the part of dmlc-core the reference depends on)."""

@@ -9,5 +9,7 @@ namespace engine {
 DeviceBackend *DeviceBackend::Create(const Config &) { return nullptr; }
 bool DeviceBackend::IsDevicePointer(const void *) { return false; }
 bool DeviceBackend::Compiled() { return false; }
+class BaseEngine;
+BaseEngine *CreateNcclEngine() { return nullptr; }
 }  // namespace engine
 }  // namespace rabit

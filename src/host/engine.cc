@@ -21,6 +21,8 @@
 namespace rabit {
 namespace engine {
 
+BaseEngine *CreateNcclEngine();  // src/device/engine_nccl.cu (stub: NULL)
+
 namespace {
 struct ThreadEngine {
   std::unique_ptr<IEngine> engine;   // what GetEngine returns after Init
@@ -52,7 +54,11 @@ bool Init(int argc, char *argv[]) {
   if (name == "robust" || name == "standard") e = new RobustEngine();
   else if (name == "mock") e = new MockEngine();
   else if (name == "base") e = new BaseEngine();
-  else utils::Error("unknown rabit_engine \"%s\" (robust|mock|base|empty)", name.c_str());
+  else if (name == "nccl") {
+    e = CreateNcclEngine();
+    utils::Check(e != nullptr, "rabit_engine=nccl needs a library built with CUDA (python build.py)");
+  }
+  else utils::Error("unknown rabit_engine \"%s\" (robust|mock|base|empty|nccl)", name.c_str());
   te->engine.reset(e);
   te->networked = e;
   if (!e->Init(argc, argv)) {

@@ -1,0 +1,71 @@
+"""The reference-compatible python module on the host engine (CPU, multi-process)."""
+import os
+import sys
+
+from conftest import ROOT, run_job, run_py
+
+
+def _py(script, args, n, **kw):
+    env = {"PYTHONPATH": ROOT + os.pathsep + os.environ.get("PYTHONPATH", "")}
+    return run_job([sys.executable, os.path.join(ROOT, script)] + list(args), n, env=env, **kw)
+
+
+def test_guide_basic_py_world4():
+    res = _py("guide/basic.py", [], 4)
+    assert res.ok, res.outputs
+    out = "".join(res.outputs.values())
+    assert out.count("after-allreduce-max: a=[3. 4. 5.]") == 4
+    assert out.count("after-allreduce-sum: a=[12. 16. 20.]") == 4
+
+
+def test_guide_broadcast_py():
+    res = _py("guide/broadcast.py", [], 3)
+    assert res.ok, res.outputs
+    assert "".join(res.outputs.values()).count("after-broadcast: s=\"{'hello world': 100, 2: 3}\"") == 3
+
+
+def test_lazy_allreduce_py_prepare_skipped_after_restart():
+    res = _py("guide/lazy_allreduce.py", ["mock=0,0,1,0"], 2)
+    assert res.ok, res.outputs
+    assert res.attempts[0] == 1
+    second_life = res.outputs[0].split("Hit Mock Error")[-1]
+    assert "run prepare function" not in second_life
+    assert "after-allreduce-sum: a=[2. 4. 6.]" in second_life
+
+
+def test_python_local_recover_with_real_kills():
+    res = _py("test/local_recover.py", ["2000", "mock=0,0,1,0", "mock=1,1,1,0", "mock=3,1,2,0", "mock=1,1,1,1"], 4,
+              timeout=180)
+    assert res.ok, {i: o[-800:] for i, o in res.outputs.items()}
+    assert res.restarts == 4
+    for o in res.outputs.values():
+        assert "iter 2 checkpointed (version 3)" in o
+
+
+def test_python_misc_api():
+    code = r'''
+import numpy as np
+from rabit_b200 import rabit
+rabit.init()
+r, n = rabit.get_rank(), rabit.get_world_size()
+assert rabit.is_distributed() and 0 <= rabit.get_ring_prev_rank() < n
+assert len(rabit.get_processor_name()) > 0
+for dt in rabit.DTYPE_ENUM__:
+    x = (np.arange(10) + r).astype(dt)
+    assert np.array_equal(rabit.allreduce(x, rabit.MAX), (np.arange(10) + n - 1).astype(dt))
+    assert np.array_equal(rabit.allreduce(x, rabit.MIN), np.arange(10).astype(dt))
+    if dt.kind in "iu":
+        assert np.array_equal(rabit.allreduce(np.full(3, 1 << r, dtype=dt), rabit.BITOR), np.full(3, (1 << n) - 1, dtype=dt))
+g = rabit.allgather(np.full(5, r, dtype=np.int32))
+assert np.array_equal(g, np.repeat(np.arange(n, dtype=np.int32), 5))
+big = np.frombuffer(bytes(range(256)) * 1024, dtype=np.uint8)      # > 64 KiB checkpoint blob (reference truncates the length)
+v, m = rabit.load_checkpoint()
+assert v == 0 and m is None
+rabit.checkpoint(big)
+assert rabit.version_number() == 1
+rabit.tracker_print("rank %d fine\n" % r)
+rabit.finalize()
+'''
+    res = run_py(code, 3)
+    assert res.ok, res.outputs
+    assert sum("fine" in m for m in res.messages) == 3
