@@ -33,8 +33,10 @@ def test_lazy_allreduce_prepare_skipped_on_recovery():
     allreduce is recovered from the peer's cache, so the prepare lambda does NOT run again."""
     res = run_job([bin_path("lazy_allreduce"), "mock=0,0,1,0"], 2)
     assert res.ok, res.outputs
-    assert res.attempts[0] == 1 and res.attempts[1] == 0
-    second_life = res.outputs[0].split("Hit Mock Error")[-1]
+    # rank 0 is whichever task reached the tracker first
+    victim = [i for i, o in res.outputs.items() if "Hit Mock Error" in o]
+    assert len(victim) == 1 and res.restarts == 1 and res.attempts[victim[0]] == 1
+    second_life = res.outputs[victim[0]].split("Hit Mock Error")[-1]
     assert "run prepare function" not in second_life
     assert "after-allreduce-max: a={1, 2, 3}" in second_life
     assert "after-allreduce-sum: a={2, 4, 6}" in second_life
