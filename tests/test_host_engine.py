@@ -118,6 +118,6 @@ def test_watchdog_kills_stuck_survivors():
     res = run_job([bin_path("model_recover"), "100", "mock=1,0,1,0", "rabit_timeout=1", "rabit_timeout_sec=2",
                    "rabit_bootstrap_cache=1"], 3, max_attempts=0, timeout=60)
     assert not res.ok
-    assert res.returncodes[1] != 0
-    assert res.returncodes[0] == 10 and res.returncodes[2] == 10
+    # which task holds rank 1 depends on arrival order at the tracker: one abort, two watchdog exits
+    assert sorted(res.returncodes.values()) == [-6, 10, 10]
     assert any("exit due to time out 2 s" in o for o in res.outputs.values())
