@@ -1,0 +1,12 @@
+#!/bin/bash
+# rabit-b200 CI entry (role of the reference's scripts/travis_script.sh): build everything, run the
+# CPU test tier, and — when a GPU is visible — the GPU tier.
+set -euo pipefail
+cd "$(dirname "$0")/.."
+python build.py
+./build/bin/unit_tests
+python -m pytest tests -x -q -m "not gpu"
+if python -c "import torch,sys; sys.exit(0 if torch.cuda.is_available() else 1)"; then
+  python -m pytest tests -x -q -m gpu
+  python __graft_entry__.py smoke
+fi

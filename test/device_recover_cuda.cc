@@ -15,6 +15,8 @@
                    cudaGetErrorString(e_), __FILE__, __LINE__); } while (0)
 
 namespace {
+struct GradPair { double g, h; };
+void PairSum(GradPair &d, const GradPair &s) { d.g += s.g; d.h += s.h; }  // NOLINT(*)
 struct DevBuf {
   float *d = nullptr; size_t n = 0;
   explicit DevBuf(size_t n_) : n(n_) { CK(cudaMalloc(&d, n * sizeof(float))); }
@@ -77,6 +79,26 @@ int main(int argc, char *argv[]) {
       for (int r = 0; r < world; ++r) want += rtest::Contribution(i, r, it, mod2) + got[i];
       rabit::utils::Check(std::fabs(want - s[i]) <= 1e-5 * std::max(1.0, std::fabs(want)),
                           "[%d] device sum mismatch at %lu (iter %d)", me, (unsigned long)i, it);  // NOLINT(*)
+    }
+    // custom struct reducer on DEVICE memory: {double g, h} pairs. First as an opaque reducer (staged
+    // through the host engine), then declared as a packed sum (fused float64 kernel); same answer.
+    for (int declared = 0; declared < 2; ++declared) {
+      const size_t np = 1000;
+      std::vector<GradPair> hp(np);
+      for (size_t i = 0; i < np; ++i) { hp[i].g = static_cast<double>((i + me + it) % 17); hp[i].h = 0.5 * me; }
+      GradPair *dp = nullptr;
+      CK(cudaMalloc(&dp, np * sizeof(GradPair)));
+      CK(cudaMemcpy(dp, hp.data(), np * sizeof(GradPair), cudaMemcpyHostToDevice));
+      rabit::Reducer<GradPair, PairSum> red;
+      if (declared) red.DeclarePackedSum<double>(2);
+      red.Allreduce(dp, np);
+      CK(cudaMemcpy(hp.data(), dp, np * sizeof(GradPair), cudaMemcpyDeviceToHost));
+      cudaFree(dp);
+      for (size_t i = 0; i < np; ++i) {
+        double g = 0, h = 0;
+        for (int r = 0; r < world; ++r) { g += static_cast<double>((i + r + it) % 17); h += 0.5 * r; }
+        rabit::utils::Check(hp[i].g == g && hp[i].h == h, "[%d] pair reducer (declared=%d) mismatch (iter %d)", me, declared, it);
+      }
     }
     for (size_t i = 0; i < n; ++i) model.w[i] = std::fmod(s[i], 1000.0f);
     rabit::CheckPoint(&model);
