@@ -31,6 +31,7 @@
 #include "coll_nvls.cuh"
 #include "coll_pipe.cuh"
 #include "coll_inplace.cuh"
+#include "coll_rounds.cuh"
 #include "device_backend.h"
 #include "../host/engine_core.h"
 #include "rabit/internal/socket.h"
