@@ -33,6 +33,7 @@ def main():
     rabit.init(sys.argv, lib="mock")
     me, world = rabit.get_rank(), rabit.get_world_size()
     assert rt.device_active(), rt.describe()
+    grow = any(a == "grow=1" for a in sys.argv)
     sym = None
     if any(a.startswith("rabit_device_heap=") for a in sys.argv):
         # collective allocation, same order on every rank (also after a restart)
@@ -101,6 +102,14 @@ def main():
                 sb.zero_()
             rt.broadcast_(sb, root)
             assert torch.equal(sb, btruth[:sb.numel()]), "[%d] symmetric broadcast mismatch iter %d" % (me, it)
+        if grow:
+            # 96 MB > the default 64 MB stage: the arena is re-allocated and re-exchanged on the fly
+            gcount = 24 * (1 << 20)
+            gx = (torch.arange(gcount, device=dev, dtype=torch.int32) % 7).float() + me
+            rabit.allreduce(gx, rabit.SUM)
+            want = (torch.arange(gcount, device=dev, dtype=torch.int32) % 7).float() * world + world * (world - 1) / 2
+            assert torch.equal(gx, want), "[%d] allreduce after arena growth mismatch iter %d" % (me, it)
+            del gx, want
         model = y % 1000.0
         rabit.checkpoint(model.cpu().numpy())
         print("[%d] iter %d checkpointed (version %d)" % (me, it, rabit.version_number()), flush=True)

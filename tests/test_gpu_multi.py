@@ -74,3 +74,10 @@ def test_device_symmetric_zero_copy_buffers(world):
     res = _run(["100000", "rabit_device_heap=64M", "mock=1,1,3,0"], world, timeout=600)
     assert res.ok, {i: o[-2500:] for i, o in res.outputs.items()}
     assert res.restarts == 1
+
+
+def test_arena_grows_on_demand(world):
+    """a message larger than the current stage makes every rank re-allocate and re-exchange its arena"""
+    res = _run(["50000", "iters=2", "grow=1"], world, timeout=600)
+    assert res.ok, {i: o[-2500:] for i, o in res.outputs.items()}
+    assert res.restarts == 0
