@@ -121,6 +121,9 @@ def finalize():
     """Leave the job and unload the engine."""
     _LIB.RabitFinalize()
     _unloadlib()
+    tb = sys.modules.get(__package__ + ".torch_binding")
+    if tb is not None:
+        tb._reset_stream_cache()
 
 
 def get_rank():

@@ -49,9 +49,22 @@ def _check(t):
         raise ValueError("rabit collectives need contiguous tensors")
 
 
+_raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+_last_stream = [None]
+
+
 def _bind_stream(lib, t):
-    if t.is_cuda:
-        lib.RabitDeviceSetStream(ctypes.c_void_p(torch.cuda.current_stream(t.device).cuda_stream))
+    """Make the engine launch on torch's current stream of the tensor's device (cheap: raw handle, and
+    the C call is skipped while the handle does not change)."""
+    if not t.is_cuda:
+        return
+    if _raw_stream is not None:
+        h = _raw_stream(t.device.index if t.device.index is not None else torch.cuda.current_device())
+    else:
+        h = torch.cuda.current_stream(t.device).cuda_stream
+    if h != _last_stream[0]:
+        lib.RabitDeviceSetStream(ctypes.c_void_p(h))
+        _last_stream[0] = h
 
 
 def describe():
@@ -60,6 +73,10 @@ def describe():
     buf = ctypes.create_string_buffer(1024)
     lib.RabitDeviceDescribe(buf, 1024)
     return buf.value.decode()
+
+
+def _reset_stream_cache():
+    _last_stream[0] = None
 
 
 def device_active():

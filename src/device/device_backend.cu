@@ -32,6 +32,7 @@
 #include "coll_pipe.cuh"
 #include "coll_inplace.cuh"
 #include "coll_rounds.cuh"
+#include "coll_ll.cuh"
 #include "device_backend.h"
 #include "../host/engine_core.h"
 #include "rabit/internal/socket.h"

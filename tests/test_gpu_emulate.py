@@ -173,3 +173,37 @@ def test_fused_consensus_mismatch_leaves_data_untouched():
 
 def test_library_kernels_were_launched():
     assert emu.launch_count() > 0
+
+
+@pytest.mark.parametrize("dtype", [torch.int8, torch.uint8, torch.int32, torch.int64, torch.float32, torch.float64])
+@pytest.mark.parametrize("op", [0, 1, 2, 3])
+@pytest.mark.parametrize("n", [2, 8])
+def test_low_latency_tagged_word_allreduce(dtype, op, n):
+    """algo 9: data and flag travel in the same 8-byte word, no barrier (<= 4 KiB per rank)"""
+    if op == 3 and dtype.is_floating_point:
+        pytest.skip("BitOR is undefined on floating point")
+    for nbytes in (8, 40, 4096):
+        count = nbytes // torch.empty((), dtype=dtype).element_size()
+        bufs = _inputs(n, count, dtype, seed=nbytes + op)
+        keeps = [torch.zeros_like(b) for b in bufs]
+        want = _reference(bufs, op)
+        assert emu.collective(emu.ALLREDUCE, bufs, algo=9, op=op, keeps=keeps) == [0] * n
+        for b, k in zip(bufs, keeps):
+            assert torch.equal(b, want) and torch.equal(k, want)
+
+
+def test_low_latency_consensus_mismatch_and_reuse():
+    n = 4
+    bufs = _inputs(n, 256, torch.float32, seed=9)
+    before = [b.clone() for b in bufs]
+    assert emu.collective(emu.ALLREDUCE, bufs, algo=9, op=2, codes=[5, 5, 5, 7]) == [1] * n
+    assert all(torch.equal(b, a) for b, a in zip(bufs, before))
+    want = _reference(bufs, 2)
+    # many back-to-back ops alternate the two slot parities; mix with a barrier kernel in between
+    assert emu.collective(emu.ALLREDUCE, bufs, algo=9, op=2) == [0] * n
+    assert all(torch.equal(b, want) for b in bufs)
+    for i in range(6):
+        bufs = _inputs(n, 100 + i, torch.float32, seed=20 + i)
+        want = _reference(bufs, 2)
+        assert emu.collective(emu.ALLREDUCE, bufs, algo=9 if i % 3 else 1, op=2) == [0] * n
+        assert all(torch.equal(b, want) for b in bufs)
