@@ -375,9 +375,22 @@ def run_reference(args):
                 print(json.dumps({"impl": "reference", "unavailable": "reference build failed: %s" % str(e)[:200]}))
             return
     if args.gpus == 1 and world == 1:
+        # With one worker the reference's Allreduce returns before touching the buffer. For orientation the
+        # same step is also run as TWO reference workers on this host's CPUs (its smallest real job).
+        info = None
+        try:
+            from rabit_b200.parallel.launcher import launch
+            res = launch([exe, str(args.bytes // 4), "2", "1", "rabit_enable_tcp_no_delay=true"], 2, capture=True,
+                         timeout=600)
+            line = [l for o in res.outputs.values() for l in o.splitlines() if l.startswith("REF_RESULT")]
+            if res.ok and line:
+                ms = float(line[0].split()[1])
+                info = {"workers": 2, "ms_per_step": ms, "aggregate_GBps": 2 * args.bytes / (ms * 1e-3) / 1e9}
+        except Exception:  # pylint: disable=broad-except
+            info = None
         print(json.dumps({"impl": "reference", "unavailable":
                           "world_size=1: rabit::Allreduce returns immediately (allreduce_robust.cc:253-256), "
-                          "there is no transfer to time"}))
+                          "there is no transfer to time", "two_host_workers_for_orientation": info}))
         return
     store = make_store(rank, world)
     tracker, port = start_tracker(rank, world, store)
