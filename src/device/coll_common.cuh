@@ -45,6 +45,10 @@ struct Control {
   unsigned long long exit_[kMaxBlocks][kMaxRanks];     // exit barrier of the in-place kernels
   unsigned long long pipe_a[kMaxBlocks][kMaxRanks];    // pipelined kernel: rounds staged by rank r
   unsigned long long pipe_b[kMaxBlocks][kMaxRanks];    // pipelined kernel: rounds reduced by rank r
+  // op counter kept ON THE DEVICE so that a captured CUDA graph can be replayed: every kernel reads it at its
+  // start and the last block to finish bumps it (kept at the end: the offsets of the rows above never move)
+  unsigned int epoch_dev;
+  unsigned int done_count;
 };
 static_assert(sizeof(Control) <= kCtrlBytes, "control block too small");
 
@@ -68,6 +72,7 @@ struct Params {
   int *status;                // host-mapped; first non-zero code wins (per emulated rank: status[r])
   unsigned long long timeout_ns;
   unsigned long long *trace;  // optional host-mapped phase timestamps of block 0 (NULL = off)
+  int device_epoch;           // 1: take the op epoch from Control::epoch_dev instead of `epoch` (graph-replayable)
 };
 
 __device__ __forceinline__ Control *CtrlOf(const Params &p, int r) {
@@ -152,6 +157,28 @@ __device__ __forceinline__ int FlagBarrier(const Params &p, int me, RowOf row_of
 __device__ __forceinline__ void Report(const Params &p, int me, int verdict) {
   if (threadIdx.x == 0 && verdict != kStOk) {
     atomicCAS(p.status + (p.emulate ? me : 0), kStOk, verdict);
+  }
+}
+
+/*! \brief first thing every kernel does: fetch the op epoch. All blocks read the same value because it is only
+ *  advanced by EndOp of the LAST block of the launch. */
+__device__ __forceinline__ void BeginOp(Params &p, int me) {  // NOLINT(*)
+  if (p.device_epoch) {
+    p.epoch = *reinterpret_cast<volatile unsigned int *>(&CtrlOf(p, me)->epoch_dev);
+  }
+}
+/*! \brief last thing every kernel does (also on the error exits): count this block; the last one advances the epoch */
+__device__ __forceinline__ void EndOp(const Params &p, int me) {
+  if (!p.device_epoch) return;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    Control *c = CtrlOf(p, me);
+    const unsigned int blocks = gridDim.x;   // in emulation every virtual rank counts its own gridDim.x blocks
+    if (atomicAdd(&c->done_count, 1u) == blocks - 1) {
+      c->done_count = 0;
+      __threadfence();
+      *reinterpret_cast<volatile unsigned int *>(&c->epoch_dev) = p.epoch + 1;
+    }
   }
 }
 

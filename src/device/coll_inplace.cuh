@@ -33,7 +33,7 @@ struct ExitRow {
 __device__ __forceinline__ char *SymOf(const Params &p, int r) { return p.arena[r] + p.sym_offset; }
 
 template <typename T, typename OP>
-__global__ void __launch_bounds__(512) TwoShotInPlace(Params p) {
+__device__ __forceinline__ void TwoShotInPlaceBody(Params &p) {
   __shared__ int s_verdict;
   const int me = p.rank;
   char *mine = SymOf(p, me);
@@ -107,12 +107,20 @@ __global__ void __launch_bounds__(512) TwoShotInPlace(Params p) {
   if (verdict != kStOk) { Report(p, me, verdict); return; }
   Stamp(p, 5);
 }
+/*! \brief launch wrapper: epoch from the control block (BeginOp), body, completion count (EndOp) */
+template <typename T, typename OP>
+__global__ void __launch_bounds__(512) TwoShotInPlace(Params p) {
+  const int me = p.emulate ? blockIdx.y : p.rank;
+  BeginOp(p, me);
+  TwoShotInPlaceBody<T, OP>(p);
+  EndOp(p, me);
+}
 
 /*! \brief switch-side reductions have a longer round trip than peer loads: keep 8 vectors per thread in flight */
 constexpr int kNvlsUnroll = 8;
 
 template <typename MM>
-__global__ void __launch_bounds__(512) NvlsInPlace(Params p) {
+__device__ __forceinline__ void NvlsInPlaceBody(Params &p) {
   __shared__ int s_verdict;
   const int me = p.rank;
   char *keep = static_cast<char *>(p.keep[0]);
@@ -157,12 +165,20 @@ __global__ void __launch_bounds__(512) NvlsInPlace(Params p) {
   }
   Stamp(p, 5);
 }
+/*! \brief launch wrapper: epoch from the control block (BeginOp), body, completion count (EndOp) */
+template <typename MM>
+__global__ void __launch_bounds__(512) NvlsInPlace(Params p) {
+  const int me = p.emulate ? blockIdx.y : p.rank;
+  BeginOp(p, me);
+  NvlsInPlaceBody<MM>(p);
+  EndOp(p, me);
+}
 
 /*!
  * \brief zero-copy broadcast: the root stores its symmetric buffer through the multicast mapping, the
  *  switch writes it into every rank's copy of the buffer; one barrier tells everybody it is complete.
  */
-__global__ void __launch_bounds__(512) NvlsBroadcastInPlace(Params p) {
+__device__ __forceinline__ void NvlsBroadcastInPlaceBody(Params &p) {
   __shared__ int s_verdict;
   const int me = p.rank;
   char *keep = static_cast<char *>(p.keep[0]);
@@ -207,6 +223,13 @@ __global__ void __launch_bounds__(512) NvlsBroadcastInPlace(Params p) {
     }
   }
 }
+/*! \brief launch wrapper: epoch from the control block (BeginOp), body, completion count (EndOp) */
+__global__ void __launch_bounds__(512) NvlsBroadcastInPlace(Params p) {
+  const int me = p.emulate ? blockIdx.y : p.rank;
+  BeginOp(p, me);
+  NvlsBroadcastInPlaceBody(p);
+  EndOp(p, me);
+}
 
 /*!
  * \brief staged broadcast through the switch, chunk-pipelined: the root streams its (ordinary) user
@@ -216,7 +239,7 @@ __global__ void __launch_bounds__(512) NvlsBroadcastInPlace(Params p) {
  */
 constexpr int kBcastRoundTiles = 4;
 
-__global__ void __launch_bounds__(512) NvlsBroadcastPipe(Params p, unsigned long long round_base) {
+__device__ __forceinline__ void NvlsBroadcastPipeBody(Params &p, unsigned long long round_base) {
   __shared__ int s_verdict;
   __shared__ int s_abort;
   const int me = p.rank;
@@ -296,6 +319,13 @@ __global__ void __launch_bounds__(512) NvlsBroadcastPipe(Params p, unsigned long
     if (s_abort != 0) Report(p, me, s_abort);
   }
 }
+/*! \brief launch wrapper: epoch from the control block (BeginOp), body, completion count (EndOp) */
+__global__ void __launch_bounds__(512) NvlsBroadcastPipe(Params p, unsigned long long round_base) {
+  const int me = p.emulate ? blockIdx.y : p.rank;
+  BeginOp(p, me);
+  NvlsBroadcastPipeBody(p, round_base);
+  EndOp(p, me);
+}
 
 /*!
  * \brief broadcast as scatter + multicast allgather. A single GPU streaming the whole buffer through
@@ -309,7 +339,7 @@ __global__ void __launch_bounds__(512) NvlsBroadcastPipe(Params p, unsigned long
  *  direct != 0 (used for 2 ranks, where re-emitting would send every byte across twice): the root
  *  simply P2P-stores every tile into every peer and the peers only wait for A.
  */
-__global__ void __launch_bounds__(512) BroadcastScatterMc(Params p, unsigned long long round_base, int inplace,
+__device__ __forceinline__ void BroadcastScatterMcBody(Params &p, unsigned long long round_base, int inplace,
                                                           int direct) {
   __shared__ int s_verdict;
   __shared__ int s_abort;
@@ -444,6 +474,14 @@ __global__ void __launch_bounds__(512) BroadcastScatterMc(Params p, unsigned lon
     }
   }
   if (s_abort != 0) Report(p, me, s_abort);
+}
+/*! \brief launch wrapper: epoch from the control block (BeginOp), body, completion count (EndOp) */
+__global__ void __launch_bounds__(512) BroadcastScatterMc(Params p, unsigned long long round_base, int inplace,
+                                                          int direct) {
+  const int me = p.emulate ? blockIdx.y : p.rank;
+  BeginOp(p, me);
+  BroadcastScatterMcBody(p, round_base, inplace, direct);
+  EndOp(p, me);
 }
 
 /*! \brief rounds BroadcastScatterMc consumes */

@@ -60,7 +60,7 @@ __device__ __forceinline__ void Emit(char *user, char *keep, size_t v, size_t nv
 }
 
 template <typename T, typename OP>
-__global__ void __launch_bounds__(512) OneShotAllreduce(Params p) {
+__device__ __forceinline__ void OneShotAllreduceBody(Params &p) {
   __shared__ int s_verdict;
   const int me = p.emulate ? blockIdx.y : p.rank;
   char *user = static_cast<char *>(p.user[p.emulate ? me : 0]);
@@ -108,9 +108,17 @@ __global__ void __launch_bounds__(512) OneShotAllreduce(Params p) {
   }
   Stamp(p, 5);
 }
+/*! \brief launch wrapper: epoch from the control block (BeginOp), body, completion count (EndOp) */
+template <typename T, typename OP>
+__global__ void __launch_bounds__(512) OneShotAllreduce(Params p) {
+  const int me = p.emulate ? blockIdx.y : p.rank;
+  BeginOp(p, me);
+  OneShotAllreduceBody<T, OP>(p);
+  EndOp(p, me);
+}
 
 template <typename T, typename OP>
-__global__ void __launch_bounds__(512) TwoShotAllreduce(Params p) {
+__device__ __forceinline__ void TwoShotAllreduceBody(Params &p) {
   __shared__ int s_verdict;
   const int me = p.emulate ? blockIdx.y : p.rank;
   char *user = static_cast<char *>(p.user[p.emulate ? me : 0]);
@@ -181,9 +189,17 @@ __global__ void __launch_bounds__(512) TwoShotAllreduce(Params p) {
   }
   Stamp(p, 5);
 }
+/*! \brief launch wrapper: epoch from the control block (BeginOp), body, completion count (EndOp) */
+template <typename T, typename OP>
+__global__ void __launch_bounds__(512) TwoShotAllreduce(Params p) {
+  const int me = p.emulate ? blockIdx.y : p.rank;
+  BeginOp(p, me);
+  TwoShotAllreduceBody<T, OP>(p);
+  EndOp(p, me);
+}
 
 /*! \brief root stages its buffer; everyone (root included, for the cache copy) pulls it */
-__global__ void __launch_bounds__(512) BroadcastPull(Params p) {
+__device__ __forceinline__ void BroadcastPullBody(Params &p) {
   __shared__ int s_verdict;
   const int me = p.emulate ? blockIdx.y : p.rank;
   char *user = static_cast<char *>(p.user[p.emulate ? me : 0]);
@@ -212,6 +228,13 @@ __global__ void __launch_bounds__(512) BroadcastPull(Params p) {
       if (v < nvec) Emit(user, keep, v, nvec_full, p.bytes, r[u], aligned);
     }
   }
+}
+/*! \brief launch wrapper: epoch from the control block (BeginOp), body, completion count (EndOp) */
+__global__ void __launch_bounds__(512) BroadcastPull(Params p) {
+  const int me = p.emulate ? blockIdx.y : p.rank;
+  BeginOp(p, me);
+  BroadcastPullBody(p);
+  EndOp(p, me);
 }
 
 /*!
@@ -256,7 +279,7 @@ __device__ __forceinline__ void CopyRangeTiles(char *dst, char *dst2, const char
  *  ranges in the API (reference allreduce_base.cc:779-843), and a rank only knows its own, so
  *  each block also writes (begin, end) into a 16-byte stage header before the barrier.
  */
-__global__ void __launch_bounds__(512) AllgatherPull(Params p) {
+__device__ __forceinline__ void AllgatherPullBody(Params &p) {
   __shared__ int s_verdict;
   const int me = p.emulate ? blockIdx.y : p.rank;
   const int ix = p.emulate ? me : 0;
@@ -283,6 +306,13 @@ __global__ void __launch_bounds__(512) AllgatherPull(Params p) {
       CopyRangeTiles(user, keep, src + kVec, b, e, p.bytes, vec_ok);
     }
   }
+}
+/*! \brief launch wrapper: epoch from the control block (BeginOp), body, completion count (EndOp) */
+__global__ void __launch_bounds__(512) AllgatherPull(Params p) {
+  const int me = p.emulate ? blockIdx.y : p.rank;
+  BeginOp(p, me);
+  AllgatherPullBody(p);
+  EndOp(p, me);
 }
 
 }  // namespace device

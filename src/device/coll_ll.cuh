@@ -58,7 +58,7 @@ __device__ __forceinline__ bool WaitTagged(const Params &p, const uint2 *addr, u
 }
 
 template <typename T, typename OP>
-__global__ void __launch_bounds__(512) OneShotLL(Params p) {
+__device__ __forceinline__ void OneShotLLBody(Params &p) {
   __shared__ int s_verdict;
   const int me = p.emulate ? blockIdx.y : p.rank;
   const int ix = p.emulate ? me : 0;
@@ -115,6 +115,14 @@ __global__ void __launch_bounds__(512) OneShotLL(Params p) {
   }
   __syncthreads();
   if (s_verdict != kStOk) Report(p, me, s_verdict);
+}
+/*! \brief launch wrapper: epoch from the control block (BeginOp), body, completion count (EndOp) */
+template <typename T, typename OP>
+__global__ void __launch_bounds__(512) OneShotLL(Params p) {
+  const int me = p.emulate ? blockIdx.y : p.rank;
+  BeginOp(p, me);
+  OneShotLLBody<T, OP>(p);
+  EndOp(p, me);
 }
 
 }  // namespace device

@@ -80,7 +80,7 @@ __device__ __forceinline__ void MultimemStore(void *mc, const uint4 &v) {
 }
 
 template <typename MM>
-__global__ void __launch_bounds__(512) NvlsAllreduce(Params p) {
+__device__ __forceinline__ void NvlsAllreduceBody(Params &p) {
   __shared__ int s_verdict;
   const int me = p.rank;  // multicast needs real peers: no single-GPU emulation
   char *user = static_cast<char *>(p.user[0]);
@@ -135,9 +135,17 @@ __global__ void __launch_bounds__(512) NvlsAllreduce(Params p) {
   }
   Stamp(p, 5);
 }
+/*! \brief launch wrapper: epoch from the control block (BeginOp), body, completion count (EndOp) */
+template <typename MM>
+__global__ void __launch_bounds__(512) NvlsAllreduce(Params p) {
+  const int me = p.emulate ? blockIdx.y : p.rank;
+  BeginOp(p, me);
+  NvlsAllreduceBody<MM>(p);
+  EndOp(p, me);
+}
 
 /*! \brief root: user -> multicast store into everybody's stage; all: barrier, local copy-out */
-__global__ void __launch_bounds__(512) NvlsBroadcast(Params p) {
+__device__ __forceinline__ void NvlsBroadcastBody(Params &p) {
   __shared__ int s_verdict;
   const int me = p.rank;
   char *user = static_cast<char *>(p.user[0]);
@@ -180,6 +188,13 @@ __global__ void __launch_bounds__(512) NvlsBroadcast(Params p) {
       if (v < nvec) Emit(user, keep, v, nvec_full, p.bytes, r[u], aligned);
     }
   }
+}
+/*! \brief launch wrapper: epoch from the control block (BeginOp), body, completion count (EndOp) */
+__global__ void __launch_bounds__(512) NvlsBroadcast(Params p) {
+  const int me = p.emulate ? blockIdx.y : p.rank;
+  BeginOp(p, me);
+  NvlsBroadcastBody(p);
+  EndOp(p, me);
 }
 
 }  // namespace device

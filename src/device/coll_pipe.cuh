@@ -67,7 +67,7 @@ __device__ __forceinline__ void GroupWait(const Params &p, const unsigned long l
 }
 
 template <typename T, typename OP, typename MM, bool kNvls>
-__global__ void __launch_bounds__(kPipeThreads, 1) PipelinedAllreduce(Params p, unsigned long long round_base) {
+__device__ __forceinline__ void PipelinedAllreduceBody(Params &p, unsigned long long round_base) {
   __shared__ int s_verdict;
   __shared__ int s_abort;
   const int me = p.emulate ? blockIdx.y : p.rank;
@@ -198,6 +198,14 @@ __global__ void __launch_bounds__(kPipeThreads, 1) PipelinedAllreduce(Params p, 
   __syncthreads();
   if (s_abort != 0) Report(p, me, s_abort);
   Stamp(p, 5);
+}
+/*! \brief launch wrapper: epoch from the control block (BeginOp), body, completion count (EndOp) */
+template <typename T, typename OP, typename MM, bool kNvls>
+__global__ void __launch_bounds__(kPipeThreads, 1) PipelinedAllreduce(Params p, unsigned long long round_base) {
+  const int me = p.emulate ? blockIdx.y : p.rank;
+  BeginOp(p, me);
+  PipelinedAllreduceBody<T, OP, MM, kNvls>(p, round_base);
+  EndOp(p, me);
 }
 
 }  // namespace device

@@ -30,7 +30,7 @@ namespace rabit {
 namespace device {
 
 template <typename T, typename OP, typename MM, bool kNvls>
-__global__ void __launch_bounds__(512) RoundsAllreduce(Params p, unsigned long long round_base) {
+__device__ __forceinline__ void RoundsAllreduceBody(Params &p, unsigned long long round_base) {
   __shared__ int s_verdict;
   __shared__ int s_abort;
   const int me = p.rank, n = p.world;
@@ -171,6 +171,14 @@ __global__ void __launch_bounds__(512) RoundsAllreduce(Params p, unsigned long l
   }
   if (s_abort != 0) Report(p, me, s_abort);
   Stamp(p, 5);
+}
+/*! \brief launch wrapper: epoch from the control block (BeginOp), body, completion count (EndOp) */
+template <typename T, typename OP, typename MM, bool kNvls>
+__global__ void __launch_bounds__(512) RoundsAllreduce(Params p, unsigned long long round_base) {
+  const int me = p.emulate ? blockIdx.y : p.rank;
+  BeginOp(p, me);
+  RoundsAllreduceBody<T, OP, MM, kNvls>(p, round_base);
+  EndOp(p, me);
 }
 
 /*! \brief rounds RoundsAllreduce consumes (identical on every rank) */

@@ -47,7 +47,7 @@ __device__ __forceinline__ void BulkLoad(void *smem_dst, const void *gmem_src, u
 
 /*! \brief dynamic shared memory: [kDepth mbarriers][kDepth][world][kSubTile] */
 template <typename T, typename OP>
-__global__ void __launch_bounds__(kTmaThreads) TwoShotAllreduceTma(Params p, int depth) {
+__device__ __forceinline__ void TwoShotAllreduceTmaBody(Params &p, int depth) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ int s_verdict;
   uint64_t *full = reinterpret_cast<uint64_t *>(smem_raw);
@@ -140,6 +140,14 @@ __global__ void __launch_bounds__(kTmaThreads) TwoShotAllreduceTma(Params p, int
     }
   }
   Stamp(p, 5);
+}
+/*! \brief launch wrapper: epoch from the control block (BeginOp), body, completion count (EndOp) */
+template <typename T, typename OP>
+__global__ void __launch_bounds__(kTmaThreads) TwoShotAllreduceTma(Params p, int depth) {
+  const int me = p.emulate ? blockIdx.y : p.rank;
+  BeginOp(p, me);
+  TwoShotAllreduceTmaBody<T, OP>(p, depth);
+  EndOp(p, me);
 }
 
 /*! \brief dynamic shared memory the TMA kernel needs for a given world and depth */

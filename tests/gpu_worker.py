@@ -34,6 +34,7 @@ def main():
     me, world = rabit.get_rank(), rabit.get_world_size()
     assert rt.device_active(), rt.describe()
     grow = any(a == "grow=1" for a in sys.argv)
+    graph = any(a == "graph=1" for a in sys.argv)
     sym = None
     if any(a.startswith("rabit_device_heap=") for a in sys.argv):
         # collective allocation, same order on every rank (also after a restart)
@@ -102,6 +103,33 @@ def main():
                 sb.zero_()
             rt.broadcast_(sb, root)
             assert torch.equal(sb, btruth[:sb.numel()]), "[%d] symmetric broadcast mismatch iter %d" % (me, it)
+        if graph:
+            # capture three small collectives once, replay them several times on every rank
+            gx = torch.zeros(2048, device=dev)
+            gy = torch.zeros(64, device=dev, dtype=torch.float64)
+            side = torch.cuda.Stream()
+            with torch.cuda.stream(side):
+                rt.allreduce_async_(gx)
+                rt.allreduce_async_(gy)
+            rt.synchronize()
+            torch.cuda.synchronize()
+            cg = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(cg, stream=side):
+                rt.allreduce_async_(gx)                 # LL kernel (<= 4 KiB? no: 8 KiB -> one-shot / NVLS)
+                rt.allreduce_async_(gy, rabit.MAX)      # LL kernel
+                rt.broadcast_async_(gx, root)
+            for rep in range(4):
+                gx.fill_(float(me + rep))
+                gy.fill_(float(me * 10 + rep))
+                torch.cuda.synchronize()
+                rabit.allreduce(np.zeros(1, dtype=np.float32), rabit.SUM)   # host barrier: every rank has refilled
+                cg.replay()
+                torch.cuda.synchronize()
+                want = float(sum(r + rep for r in range(world)))
+                assert torch.equal(gx, torch.full_like(gx, want)), "[%d] graph replay %d allreduce mismatch" % (me, rep)
+                assert torch.equal(gy, torch.full_like(gy, float((world - 1) * 10 + rep))), "[%d] graph max mismatch" % me
+            rt.allreduce_async_(gx)                     # eager op after the replays
+            rt.synchronize()
         if grow:
             # 96 MB > the default 64 MB stage: the arena is re-allocated and re-exchanged on the fly
             gcount = 24 * (1 << 20)

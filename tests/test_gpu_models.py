@@ -34,3 +34,37 @@ def test_histogram_allreducer_single_gpu():
         assert rabit.version_number() == 1
     finally:
         rabit.finalize()
+
+
+def test_collectives_replay_from_a_cuda_graph():
+    """The op epoch lives in device memory, so a captured graph of collectives can be replayed and
+    freely mixed with eager launches (world of one, kernels forced on)."""
+    from rabit_b200 import rabit, torch_binding as rt
+    torch.cuda.set_device(0)
+    rabit.init(["rabit_device=on", "rabit_device_force=1"])
+    try:
+        x = torch.arange(10000, device="cuda", dtype=torch.float32)
+        y = torch.ones(300, device="cuda", dtype=torch.float64)
+        side = torch.cuda.Stream()
+        with torch.cuda.stream(side):
+            rt.allreduce_async_(x)          # warm up outside capture (arena sizing, lazy init)
+            rt.allreduce_async_(y)
+        rt.synchronize()
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        before = rt.launch_count()
+        with torch.cuda.graph(g, stream=side):
+            rt.allreduce_async_(x)
+            rt.allreduce_async_(y, rabit.MAX)
+            rt.broadcast_async_(x, 0)
+        captured = rt.launch_count() - before
+        assert captured == 3
+        for _ in range(5):
+            g.replay()
+        torch.cuda.synchronize()
+        rt.allreduce_async_(x)              # eager launch after replays: the epochs still line up
+        rt.synchronize()
+        assert torch.equal(x, torch.arange(10000, device="cuda", dtype=torch.float32))
+        assert torch.equal(y, torch.ones(300, device="cuda", dtype=torch.float64))
+    finally:
+        rabit.finalize()

@@ -81,3 +81,9 @@ def test_arena_grows_on_demand(world):
     res = _run(["50000", "iters=2", "grow=1"], world, timeout=600)
     assert res.ok, {i: o[-2500:] for i, o in res.outputs.items()}
     assert res.restarts == 0
+
+
+def test_cuda_graph_replay_across_ranks(world):
+    """collectives captured in a CUDA graph and replayed on every rank (device-side op epoch)"""
+    res = _run(["20000", "iters=2", "graph=1"], world, timeout=600)
+    assert res.ok, {i: o[-2500:] for i, o in res.outputs.items()}
