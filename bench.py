@@ -267,6 +267,20 @@ def run_ours(args):
                 t = timed(lambda: rt.allreduce_async_(vs), it, 3)
                 row["allreduce_sym_us"] = t * 1e3
                 row["allreduce_sym_busbw_GBps"] = sz / (t * 1e-3) / 1e9 * (2.0 * (n - 1) / n)
+            if sz <= (4 << 20):
+                # launch-bound sizes: the same op replayed from a CUDA graph of 20 launches (no host work per op)
+                side = torch.cuda.Stream()
+                with torch.cuda.stream(side):
+                    rt.allreduce_async_(vs)
+                rt.synchronize()
+                torch.cuda.synchronize()
+                cg = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(cg, stream=side):
+                    for _ in range(20):
+                        rt.allreduce_async_(vs)
+                t = timed(cg.replay, 5, 2) / 20.0
+                row["allreduce_graph_us"] = t * 1e3
+                del cg
             t = timed(lambda: rt.broadcast_async_(v, 0), it, 3)
             row["broadcast_us"] = t * 1e3
             row["broadcast_busbw_GBps"] = sz / (t * 1e-3) / 1e9

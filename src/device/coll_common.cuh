@@ -75,14 +75,25 @@ struct Params {
   int device_epoch;           // 1: take the op epoch from Control::epoch_dev instead of `epoch` (graph-replayable)
 };
 
+/*! \brief the op epoch of the running kernel. With device_epoch it was fetched from the control block by BeginOp
+ *  into ONE shared word per block (Params stays untouched in the constant bank: writing into it would make the
+ *  compiler spill the whole 800-byte struct to local memory in every thread). */
+__device__ __forceinline__ unsigned int &SharedEpoch() {
+  __shared__ unsigned int epoch_of_this_launch;
+  return epoch_of_this_launch;
+}
+__device__ __forceinline__ unsigned int OpEpoch(const Params &p) {
+  return p.device_epoch ? SharedEpoch() : p.epoch;
+}
+
 __device__ __forceinline__ Control *CtrlOf(const Params &p, int r) {
   return reinterpret_cast<Control *>(p.arena[r]);
 }
 __device__ __forceinline__ char *StageOf(const Params &p, int r) {
-  return p.arena[r] + kCtrlBytes + static_cast<size_t>(p.epoch & 1u) * p.stage_bytes;
+  return p.arena[r] + kCtrlBytes + static_cast<size_t>(OpEpoch(p) & 1u) * p.stage_bytes;
 }
 __device__ __forceinline__ char *McStage(const Params &p) {
-  return p.mc_arena + kCtrlBytes + static_cast<size_t>(p.epoch & 1u) * p.stage_bytes;
+  return p.mc_arena + kCtrlBytes + static_cast<size_t>(OpEpoch(p) & 1u) * p.stage_bytes;
 }
 
 __device__ __forceinline__ unsigned long long GlobalTimer() {
@@ -162,9 +173,10 @@ __device__ __forceinline__ void Report(const Params &p, int me, int verdict) {
 
 /*! \brief first thing every kernel does: fetch the op epoch. All blocks read the same value because it is only
  *  advanced by EndOp of the LAST block of the launch. */
-__device__ __forceinline__ void BeginOp(Params &p, int me) {  // NOLINT(*)
+__device__ __forceinline__ void BeginOp(const Params &p, int me) {
   if (p.device_epoch) {
-    p.epoch = *reinterpret_cast<volatile unsigned int *>(&CtrlOf(p, me)->epoch_dev);
+    if (threadIdx.x == 0) SharedEpoch() = *reinterpret_cast<volatile unsigned int *>(&CtrlOf(p, me)->epoch_dev);
+    __syncthreads();
   }
 }
 /*! \brief last thing every kernel does (also on the error exits): count this block; the last one advances the epoch */
@@ -177,7 +189,7 @@ __device__ __forceinline__ void EndOp(const Params &p, int me) {
     if (atomicAdd(&c->done_count, 1u) == blocks - 1) {
       c->done_count = 0;
       __threadfence();
-      *reinterpret_cast<volatile unsigned int *>(&c->epoch_dev) = p.epoch + 1;
+      *reinterpret_cast<volatile unsigned int *>(&c->epoch_dev) = OpEpoch(p) + 1;
     }
   }
 }

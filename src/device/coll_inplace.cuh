@@ -33,13 +33,13 @@ struct ExitRow {
 __device__ __forceinline__ char *SymOf(const Params &p, int r) { return p.arena[r] + p.sym_offset; }
 
 template <typename T, typename OP>
-__device__ __forceinline__ void TwoShotInPlaceBody(Params &p) {
+__device__ __forceinline__ void TwoShotInPlaceBody(const Params &p) {
   __shared__ int s_verdict;
   const int me = p.rank;
   char *mine = SymOf(p, me);
   char *keep = static_cast<char *>(p.keep[0]);
   Stamp(p, 0);
-  int verdict = FlagBarrier(p, me, EntryRow{p.epoch & 1u}, p.epoch + 1, p.code[0], true, &s_verdict);
+  int verdict = FlagBarrier(p, me, EntryRow{OpEpoch(p) & 1u}, OpEpoch(p) + 1, p.code[0], true, &s_verdict);
   if (verdict != kStOk) { Report(p, me, verdict); return; }
   Stamp(p, 2);
   // symmetric buffers are allocated in 256-byte units, so the padded last vector is addressable
@@ -80,7 +80,7 @@ __device__ __forceinline__ void TwoShotInPlaceBody(Params &p) {
     }
   }
   Stamp(p, 3);
-  verdict = FlagBarrier(p, me, MidRow{}, p.epoch + 1, 0u, false, &s_verdict);
+  verdict = FlagBarrier(p, me, MidRow{}, OpEpoch(p) + 1, 0u, false, &s_verdict);
   if (verdict != kStOk) { Report(p, me, verdict); return; }
   Stamp(p, 4);
   for (size_t tile = blockIdx.x, k = 0; tile < ntiles; tile += gridDim.x, ++k) {
@@ -103,7 +103,7 @@ __device__ __forceinline__ void TwoShotInPlaceBody(Params &p) {
       }
     }
   }
-  verdict = FlagBarrier(p, me, ExitRow{}, p.epoch + 1, 0u, false, &s_verdict);
+  verdict = FlagBarrier(p, me, ExitRow{}, OpEpoch(p) + 1, 0u, false, &s_verdict);
   if (verdict != kStOk) { Report(p, me, verdict); return; }
   Stamp(p, 5);
 }
@@ -120,13 +120,13 @@ __global__ void __launch_bounds__(512) TwoShotInPlace(Params p) {
 constexpr int kNvlsUnroll = 8;
 
 template <typename MM>
-__device__ __forceinline__ void NvlsInPlaceBody(Params &p) {
+__device__ __forceinline__ void NvlsInPlaceBody(const Params &p) {
   __shared__ int s_verdict;
   const int me = p.rank;
   char *keep = static_cast<char *>(p.keep[0]);
   char *mc = p.mc_arena + p.sym_offset;
   Stamp(p, 0);
-  int verdict = FlagBarrier(p, me, EntryRow{p.epoch & 1u}, p.epoch + 1, p.code[0], true, &s_verdict);
+  int verdict = FlagBarrier(p, me, EntryRow{OpEpoch(p) & 1u}, OpEpoch(p) + 1, p.code[0], true, &s_verdict);
   if (verdict != kStOk) { Report(p, me, verdict); return; }
   Stamp(p, 2);
   const size_t nvec = (p.bytes + kVec - 1) / kVec;
@@ -149,7 +149,7 @@ __device__ __forceinline__ void NvlsInPlaceBody(Params &p) {
     }
   }
   Stamp(p, 3);
-  verdict = FlagBarrier(p, me, MidRow{}, p.epoch + 1, 0u, false, &s_verdict);
+  verdict = FlagBarrier(p, me, MidRow{}, OpEpoch(p) + 1, 0u, false, &s_verdict);
   if (verdict != kStOk) { Report(p, me, verdict); return; }
   Stamp(p, 4);
   if (keep != nullptr) {
@@ -178,7 +178,7 @@ __global__ void __launch_bounds__(512) NvlsInPlace(Params p) {
  * \brief zero-copy broadcast: the root stores its symmetric buffer through the multicast mapping, the
  *  switch writes it into every rank's copy of the buffer; one barrier tells everybody it is complete.
  */
-__device__ __forceinline__ void NvlsBroadcastInPlaceBody(Params &p) {
+__device__ __forceinline__ void NvlsBroadcastInPlaceBody(const Params &p) {
   __shared__ int s_verdict;
   const int me = p.rank;
   char *keep = static_cast<char *>(p.keep[0]);
@@ -186,7 +186,7 @@ __device__ __forceinline__ void NvlsBroadcastInPlaceBody(Params &p) {
   const size_t tile_vecs = static_cast<size_t>(blockDim.x) * kNvlsUnroll;
   const size_t ntiles = (nvec + tile_vecs - 1) / tile_vecs;
   // nobody may still be using the previous contents of its buffer when the root starts overwriting it
-  int verdict = FlagBarrier(p, me, EntryRow{p.epoch & 1u}, p.epoch + 1, p.code[0], true, &s_verdict);
+  int verdict = FlagBarrier(p, me, EntryRow{OpEpoch(p) & 1u}, OpEpoch(p) + 1, p.code[0], true, &s_verdict);
   if (verdict != kStOk) { Report(p, me, verdict); return; }
   if (me == p.root) {
     const char *src = SymOf(p, me);
@@ -209,7 +209,7 @@ __device__ __forceinline__ void NvlsBroadcastInPlaceBody(Params &p) {
       }
     }
   }
-  verdict = FlagBarrier(p, me, MidRow{}, p.epoch + 1, 0u, false, &s_verdict);
+  verdict = FlagBarrier(p, me, MidRow{}, OpEpoch(p) + 1, 0u, false, &s_verdict);
   if (verdict != kStOk) { Report(p, me, verdict); return; }
   if (me != p.root && keep != nullptr) {
     const char *src = SymOf(p, me);
@@ -239,7 +239,7 @@ __global__ void __launch_bounds__(512) NvlsBroadcastInPlace(Params p) {
  */
 constexpr int kBcastRoundTiles = 4;
 
-__device__ __forceinline__ void NvlsBroadcastPipeBody(Params &p, unsigned long long round_base) {
+__device__ __forceinline__ void NvlsBroadcastPipeBody(const Params &p, unsigned long long round_base) {
   __shared__ int s_verdict;
   __shared__ int s_abort;
   const int me = p.rank;
@@ -253,7 +253,7 @@ __device__ __forceinline__ void NvlsBroadcastPipeBody(Params &p, unsigned long l
   const size_t rounds = (chan_tiles + kBcastRoundTiles - 1) / kBcastRoundTiles;
   if (threadIdx.x == 0) s_abort = 0;
   // stage[parity] of every rank is free once everybody has entered this op (see coll_common.cuh)
-  int verdict = FlagBarrier(p, me, EntryRow{p.epoch & 1u}, p.epoch + 1, p.code[0], true, &s_verdict);
+  int verdict = FlagBarrier(p, me, EntryRow{OpEpoch(p) & 1u}, OpEpoch(p) + 1, p.code[0], true, &s_verdict);
   if (verdict != kStOk) { Report(p, me, verdict); return; }
   if (me == p.root) {
     char *mc = McStage(p);
@@ -339,7 +339,7 @@ __global__ void __launch_bounds__(512) NvlsBroadcastPipe(Params p, unsigned long
  *  direct != 0 (used for 2 ranks, where re-emitting would send every byte across twice): the root
  *  simply P2P-stores every tile into every peer and the peers only wait for A.
  */
-__device__ __forceinline__ void BroadcastScatterMcBody(Params &p, unsigned long long round_base, int inplace,
+__device__ __forceinline__ void BroadcastScatterMcBody(const Params &p, unsigned long long round_base, int inplace,
                                                           int direct) {
   __shared__ int s_verdict;
   __shared__ int s_abort;
@@ -353,7 +353,7 @@ __device__ __forceinline__ void BroadcastScatterMcBody(Params &p, unsigned long 
   const size_t chan_tiles = ntiles > static_cast<size_t>(b) ? (ntiles - b + G - 1) / G : 0;
   const size_t rounds = (chan_tiles + n - 1) / n;
   if (threadIdx.x == 0) s_abort = 0;
-  int verdict = FlagBarrier(p, me, EntryRow{p.epoch & 1u}, p.epoch + 1, p.code[0], true, &s_verdict);
+  int verdict = FlagBarrier(p, me, EntryRow{OpEpoch(p) & 1u}, OpEpoch(p) + 1, p.code[0], true, &s_verdict);
   if (verdict != kStOk) { Report(p, me, verdict); return; }
   char *my_dst = inplace ? SymOf(p, me) : StageOf(p, me);
   char *mc_dst = inplace ? p.mc_arena + p.sym_offset : McStage(p);

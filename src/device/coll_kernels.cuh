@@ -60,7 +60,7 @@ __device__ __forceinline__ void Emit(char *user, char *keep, size_t v, size_t nv
 }
 
 template <typename T, typename OP>
-__device__ __forceinline__ void OneShotAllreduceBody(Params &p) {
+__device__ __forceinline__ void OneShotAllreduceBody(const Params &p) {
   __shared__ int s_verdict;
   const int me = p.emulate ? blockIdx.y : p.rank;
   char *user = static_cast<char *>(p.user[p.emulate ? me : 0]);
@@ -69,7 +69,7 @@ __device__ __forceinline__ void OneShotAllreduceBody(Params &p) {
   Stamp(p, 0);
   CopyTiles<true>(user, StageOf(p, me), p.bytes, aligned);
   Stamp(p, 1);
-  int verdict = FlagBarrier(p, me, EntryRow{p.epoch & 1u}, p.epoch + 1, p.code[p.emulate ? me : 0], true, &s_verdict);
+  int verdict = FlagBarrier(p, me, EntryRow{OpEpoch(p) & 1u}, OpEpoch(p) + 1, p.code[p.emulate ? me : 0], true, &s_verdict);
   if (verdict != kStOk) { Report(p, me, verdict); return; }
   Stamp(p, 2);
 
@@ -118,7 +118,7 @@ __global__ void __launch_bounds__(512) OneShotAllreduce(Params p) {
 }
 
 template <typename T, typename OP>
-__device__ __forceinline__ void TwoShotAllreduceBody(Params &p) {
+__device__ __forceinline__ void TwoShotAllreduceBody(const Params &p) {
   __shared__ int s_verdict;
   const int me = p.emulate ? blockIdx.y : p.rank;
   char *user = static_cast<char *>(p.user[p.emulate ? me : 0]);
@@ -127,7 +127,7 @@ __device__ __forceinline__ void TwoShotAllreduceBody(Params &p) {
   Stamp(p, 0);
   CopyTiles<true>(user, StageOf(p, me), p.bytes, aligned);
   Stamp(p, 1);
-  int verdict = FlagBarrier(p, me, EntryRow{p.epoch & 1u}, p.epoch + 1, p.code[p.emulate ? me : 0], true, &s_verdict);
+  int verdict = FlagBarrier(p, me, EntryRow{OpEpoch(p) & 1u}, OpEpoch(p) + 1, p.code[p.emulate ? me : 0], true, &s_verdict);
   if (verdict != kStOk) { Report(p, me, verdict); return; }
   Stamp(p, 2);
 
@@ -168,7 +168,7 @@ __device__ __forceinline__ void TwoShotAllreduceBody(Params &p) {
     }
   }
   Stamp(p, 3);
-  verdict = FlagBarrier(p, me, MidRow{}, p.epoch + 1, 0u, false, &s_verdict);
+  verdict = FlagBarrier(p, me, MidRow{}, OpEpoch(p) + 1, 0u, false, &s_verdict);
   if (verdict != kStOk) { Report(p, me, verdict); return; }
   Stamp(p, 4);
   // allgather: pull every tile from its owner's stage
@@ -199,14 +199,14 @@ __global__ void __launch_bounds__(512) TwoShotAllreduce(Params p) {
 }
 
 /*! \brief root stages its buffer; everyone (root included, for the cache copy) pulls it */
-__device__ __forceinline__ void BroadcastPullBody(Params &p) {
+__device__ __forceinline__ void BroadcastPullBody(const Params &p) {
   __shared__ int s_verdict;
   const int me = p.emulate ? blockIdx.y : p.rank;
   char *user = static_cast<char *>(p.user[p.emulate ? me : 0]);
   char *keep = static_cast<char *>(p.keep[p.emulate ? me : 0]);
   const bool aligned = (reinterpret_cast<uintptr_t>(user) % kVec) == 0;
   if (me == p.root) CopyTiles<true>(user, StageOf(p, me), p.bytes, aligned);
-  int verdict = FlagBarrier(p, me, EntryRow{p.epoch & 1u}, p.epoch + 1, p.code[p.emulate ? me : 0], true, &s_verdict);
+  int verdict = FlagBarrier(p, me, EntryRow{OpEpoch(p) & 1u}, OpEpoch(p) + 1, p.code[p.emulate ? me : 0], true, &s_verdict);
   if (verdict != kStOk) { Report(p, me, verdict); return; }
   if (me == p.root && keep == nullptr) return;
   const size_t nvec_full = p.bytes / kVec;
@@ -279,7 +279,7 @@ __device__ __forceinline__ void CopyRangeTiles(char *dst, char *dst2, const char
  *  ranges in the API (reference allreduce_base.cc:779-843), and a rank only knows its own, so
  *  each block also writes (begin, end) into a 16-byte stage header before the barrier.
  */
-__device__ __forceinline__ void AllgatherPullBody(Params &p) {
+__device__ __forceinline__ void AllgatherPullBody(const Params &p) {
   __shared__ int s_verdict;
   const int me = p.emulate ? blockIdx.y : p.rank;
   const int ix = p.emulate ? me : 0;
@@ -293,7 +293,7 @@ __device__ __forceinline__ void AllgatherPullBody(Params &p) {
     reinterpret_cast<volatile unsigned long long *>(stage)[1] = end;
   }
   CopyRangeTiles(stage + kVec, nullptr, user, begin, end, p.bytes, vec_ok);
-  int verdict = FlagBarrier(p, me, EntryRow{p.epoch & 1u}, p.epoch + 1, p.code[ix], true, &s_verdict);
+  int verdict = FlagBarrier(p, me, EntryRow{OpEpoch(p) & 1u}, OpEpoch(p) + 1, p.code[ix], true, &s_verdict);
   if (verdict != kStOk) { Report(p, me, verdict); return; }
   const int n = p.world;
   for (int r = 0; r < n; ++r) {

@@ -31,7 +31,7 @@ constexpr size_t kLLBytes = 2 * kMaxRanks * kLLSlotBytes;              // two pa
 /*! \brief rank r's LL area: [parity][source rank][word] of {value, tag} */
 __device__ __forceinline__ uint2 *LLSlot(const Params &p, int r, int src) {
   char *base = p.arena[r] + kCtrlBytes + 2 * p.stage_bytes;
-  return reinterpret_cast<uint2 *>(base) + (static_cast<size_t>(p.epoch & 1u) * kMaxRanks + src) * kLLSlotWords;
+  return reinterpret_cast<uint2 *>(base) + (static_cast<size_t>(OpEpoch(p) & 1u) * kMaxRanks + src) * kLLSlotWords;
 }
 __device__ __forceinline__ void StoreTagged(uint2 *addr, unsigned int value, unsigned int tag) {
   asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1, %2};" ::"l"(addr), "r"(value), "r"(tag) : "memory");
@@ -58,14 +58,14 @@ __device__ __forceinline__ bool WaitTagged(const Params &p, const uint2 *addr, u
 }
 
 template <typename T, typename OP>
-__device__ __forceinline__ void OneShotLLBody(Params &p) {
+__device__ __forceinline__ void OneShotLLBody(const Params &p) {
   __shared__ int s_verdict;
   const int me = p.emulate ? blockIdx.y : p.rank;
   const int ix = p.emulate ? me : 0;
   const int n = p.world;
   unsigned int *user = static_cast<unsigned int *>(p.user[ix]);
   unsigned int *keep = static_cast<unsigned int *>(p.keep[ix]);
-  const unsigned int tag = p.epoch + 1;
+  const unsigned int tag = OpEpoch(p) + 1;
   const unsigned int words = static_cast<unsigned int>(p.bytes / 4);
   constexpr unsigned int kUnitWords = sizeof(T) > 4 ? 2 : 1;   // an element never straddles two threads
   const unsigned int units = words / kUnitWords;

@@ -80,7 +80,7 @@ __device__ __forceinline__ void MultimemStore(void *mc, const uint4 &v) {
 }
 
 template <typename MM>
-__device__ __forceinline__ void NvlsAllreduceBody(Params &p) {
+__device__ __forceinline__ void NvlsAllreduceBody(const Params &p) {
   __shared__ int s_verdict;
   const int me = p.rank;  // multicast needs real peers: no single-GPU emulation
   char *user = static_cast<char *>(p.user[0]);
@@ -89,7 +89,7 @@ __device__ __forceinline__ void NvlsAllreduceBody(Params &p) {
   Stamp(p, 0);
   CopyTiles<true>(user, StageOf(p, me), p.bytes, aligned);
   Stamp(p, 1);
-  int verdict = FlagBarrier(p, me, EntryRow{p.epoch & 1u}, p.epoch + 1, p.code[0], true, &s_verdict);
+  int verdict = FlagBarrier(p, me, EntryRow{OpEpoch(p) & 1u}, OpEpoch(p) + 1, p.code[0], true, &s_verdict);
   if (verdict != kStOk) { Report(p, me, verdict); return; }
   Stamp(p, 2);
   const size_t nvec_full = p.bytes / kVec;
@@ -114,7 +114,7 @@ __device__ __forceinline__ void NvlsAllreduceBody(Params &p) {
     }
   }
   Stamp(p, 3);
-  verdict = FlagBarrier(p, me, MidRow{}, p.epoch + 1, 0u, false, &s_verdict);
+  verdict = FlagBarrier(p, me, MidRow{}, OpEpoch(p) + 1, 0u, false, &s_verdict);
   if (verdict != kStOk) { Report(p, me, verdict); return; }
   Stamp(p, 4);
   // every tile of this channel now sits, fully reduced, in OUR stage: local copy-out
@@ -145,7 +145,7 @@ __global__ void __launch_bounds__(512) NvlsAllreduce(Params p) {
 }
 
 /*! \brief root: user -> multicast store into everybody's stage; all: barrier, local copy-out */
-__device__ __forceinline__ void NvlsBroadcastBody(Params &p) {
+__device__ __forceinline__ void NvlsBroadcastBody(const Params &p) {
   __shared__ int s_verdict;
   const int me = p.rank;
   char *user = static_cast<char *>(p.user[0]);
@@ -170,7 +170,7 @@ __device__ __forceinline__ void NvlsBroadcastBody(Params &p) {
       }
     }
   }
-  int verdict = FlagBarrier(p, me, EntryRow{p.epoch & 1u}, p.epoch + 1, p.code[0], true, &s_verdict);
+  int verdict = FlagBarrier(p, me, EntryRow{OpEpoch(p) & 1u}, OpEpoch(p) + 1, p.code[0], true, &s_verdict);
   if (verdict != kStOk) { Report(p, me, verdict); return; }
   if (me == p.root && keep == nullptr) return;
   const char *src = StageOf(p, me);

@@ -67,7 +67,7 @@ __device__ __forceinline__ void GroupWait(const Params &p, const unsigned long l
 }
 
 template <typename T, typename OP, typename MM, bool kNvls>
-__device__ __forceinline__ void PipelinedAllreduceBody(Params &p, unsigned long long round_base) {
+__device__ __forceinline__ void PipelinedAllreduceBody(const Params &p, unsigned long long round_base) {
   __shared__ int s_verdict;
   __shared__ int s_abort;
   const int me = p.emulate ? blockIdx.y : p.rank;
@@ -77,7 +77,7 @@ __device__ __forceinline__ void PipelinedAllreduceBody(Params &p, unsigned long 
   if (threadIdx.x == 0) s_abort = 0;
   Stamp(p, 0);
   // consensus + "everybody is here" before any byte moves
-  int verdict = FlagBarrier(p, me, EntryRow{p.epoch & 1u}, p.epoch + 1, p.code[ix], true, &s_verdict);
+  int verdict = FlagBarrier(p, me, EntryRow{OpEpoch(p) & 1u}, OpEpoch(p) + 1, p.code[ix], true, &s_verdict);
   if (verdict != kStOk) { Report(p, me, verdict); return; }
   Stamp(p, 1);
 

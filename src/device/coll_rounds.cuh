@@ -30,7 +30,7 @@ namespace rabit {
 namespace device {
 
 template <typename T, typename OP, typename MM, bool kNvls>
-__device__ __forceinline__ void RoundsAllreduceBody(Params &p, unsigned long long round_base) {
+__device__ __forceinline__ void RoundsAllreduceBody(const Params &p, unsigned long long round_base) {
   __shared__ int s_verdict;
   __shared__ int s_abort;
   const int me = p.rank, n = p.world;
@@ -44,7 +44,7 @@ __device__ __forceinline__ void RoundsAllreduceBody(Params &p, unsigned long lon
   const size_t rounds = (chan_tiles + n - 1) / n;
   if (threadIdx.x == 0) s_abort = 0;
   Stamp(p, 0);
-  int verdict = FlagBarrier(p, me, EntryRow{p.epoch & 1u}, p.epoch + 1, p.code[0], true, &s_verdict);
+  int verdict = FlagBarrier(p, me, EntryRow{OpEpoch(p) & 1u}, OpEpoch(p) + 1, p.code[0], true, &s_verdict);
   if (verdict != kStOk) { Report(p, me, verdict); return; }
   Stamp(p, 1);
   char *my_stage = StageOf(p, me);

@@ -47,7 +47,7 @@ __device__ __forceinline__ void BulkLoad(void *smem_dst, const void *gmem_src, u
 
 /*! \brief dynamic shared memory: [kDepth mbarriers][kDepth][world][kSubTile] */
 template <typename T, typename OP>
-__device__ __forceinline__ void TwoShotAllreduceTmaBody(Params &p, int depth) {
+__device__ __forceinline__ void TwoShotAllreduceTmaBody(const Params &p, int depth) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ int s_verdict;
   uint64_t *full = reinterpret_cast<uint64_t *>(smem_raw);
@@ -64,7 +64,7 @@ __device__ __forceinline__ void TwoShotAllreduceTmaBody(Params &p, int depth) {
   Stamp(p, 0);
   CopyTiles<true>(user, StageOf(p, me), p.bytes, aligned);
   Stamp(p, 1);
-  int verdict = FlagBarrier(p, me, EntryRow{p.epoch & 1u}, p.epoch + 1, p.code[p.emulate ? me : 0], true, &s_verdict);
+  int verdict = FlagBarrier(p, me, EntryRow{OpEpoch(p) & 1u}, OpEpoch(p) + 1, p.code[p.emulate ? me : 0], true, &s_verdict);
   if (verdict != kStOk) { Report(p, me, verdict); return; }
   Stamp(p, 2);
 
@@ -120,7 +120,7 @@ __device__ __forceinline__ void TwoShotAllreduceTmaBody(Params &p, int depth) {
     __syncthreads();
   }
   Stamp(p, 3);
-  verdict = FlagBarrier(p, me, MidRow{}, p.epoch + 1, 0u, false, &s_verdict);
+  verdict = FlagBarrier(p, me, MidRow{}, OpEpoch(p) + 1, 0u, false, &s_verdict);
   if (verdict != kStOk) { Report(p, me, verdict); return; }
   Stamp(p, 4);
   const size_t tile_vecs = static_cast<size_t>(blockDim.x) * kUnroll;
