@@ -39,6 +39,7 @@ class _Conn(object):
         self.cmd = ""
         self.port = -1
         self.wait_accept = 0
+        self.pending = set()      # ranks this worker still expects to be dialled by
 
     def recv_all(self, n):
         chunks = []
@@ -182,12 +183,15 @@ class Tracker(object):
             if c.recv_int() != 0:
                 continue
             c.port = c.recv_int()
+            # book-keeping by SET, not by count: a worker that restarts its rendezvous dials the same parked
+            # peer a second time, which must not use up the slot of somebody the peer is still waiting for
             for r in dial:
-                wait_conn[r].wait_accept -= 1
-                if wait_conn[r].wait_accept == 0:
+                wait_conn[r].pending.discard(rank)
+                if not wait_conn[r].pending:
                     del wait_conn[r]
-            c.wait_accept = len(bad) - len(dial)
-            if c.wait_accept > 0:
+            c.pending = set(bad) - set(dial)
+            c.wait_accept = len(c.pending)
+            if c.pending:
                 wait_conn[rank] = c
             return
 
@@ -240,6 +244,8 @@ class Tracker(object):
                         pending = []
                     continue
                 # a restarted worker ("start") or a survivor re-joining ("recover")
+                log.debug("%s rank %d (task %s); parked: %s", c.cmd, rank, c.task_id,
+                          {r: sorted(w.pending) for r, w in wait_conn.items()})
                 wait_conn.pop(rank, None)
                 self._assign(c, rank, tree, parent, ring, wait_conn)
             except (ConnectionError, OSError, struct.error) as e:

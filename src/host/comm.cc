@@ -11,6 +11,8 @@ namespace rabit {
 namespace engine {
 
 namespace {
+/*! \brief idle time after which a blocked primitive probes every link for a silent death */
+const int kProbeMs = 100;
 /*! \brief handshake cookie of the tracker protocol (reference allreduce_base.h kMagic) */
 const int kTrackerMagic = 0xff99;
 
@@ -59,7 +61,13 @@ const char *StatusName(Status s) {
 HostComm::HostComm() {}
 HostComm::~HostComm() { this->CloseLinks(); }
 
-void HostComm::CloseLinks() {
+void HostComm::CloseLinks(bool graceful) {
+  if (graceful) {
+    // orderly exit: leave one "bye" byte behind, so that a neighbour that is still inside its last collective
+    // can tell this close from a crash (see LinksBroken)
+    const char bye = 'B';
+    for (Link &l : links_) if (!l.sock.IsClosed()) l.sock.Send(&bye, 1);
+  }
   for (Link &l : links_) l.sock.Close();
   links_.clear();
   tree_.clear();
@@ -70,15 +78,12 @@ void HostComm::CloseLinks() {
 bool HostComm::LinksBroken() {
   for (Link &l : links_) {
     if (l.sock.IsClosed()) return true;
-    pollfd pf; pf.fd = l.sock.fd; pf.events = POLLIN | POLLRDHUP; pf.revents = 0;
-    if (poll(&pf, 1, 0) <= 0) continue;
-    if (pf.revents & (POLLERR | POLLHUP | POLLRDHUP | POLLNVAL)) return true;
-    if (pf.revents & POLLIN) {
-      char c;
-      ssize_t n = recv(l.sock.fd, &c, 1, MSG_PEEK | MSG_DONTWAIT);
-      if (n == 0) return true;
-      if (n < 0 && !WouldBlock()) return true;
-    }
+    // peek: 0 = the peer closed without saying bye (it died, or it tore its links down to recover);
+    // pending bytes (payload of a running op, or the bye of a peer that finished) = fine
+    char c;
+    ssize_t n = recv(l.sock.fd, &c, 1, MSG_PEEK | MSG_DONTWAIT);
+    if (n == 0) return true;
+    if (n < 0 && !WouldBlock()) return true;
   }
   return false;
 }
@@ -132,6 +137,7 @@ bool HostComm::Connect(const char *cmd) {
     utils::Check(t.RecvInt(&ring_prev_rank) && t.RecvInt(&ring_next_rank), "tracker: cannot read ring");
 
     utils::TCPSocket listener;
+    struct CloseOnExit { utils::TCPSocket *s; ~CloseOnExit() { s->Close(); } } close_listener{&listener};
     listener.Create();
     int port;
     if (cfg.slave_port > 0) {
@@ -143,6 +149,7 @@ bool HostComm::Connect(const char *cmd) {
     listener.Listen();
 
     int nconn = 0, naccept = 0, nerr = 0;
+    std::vector<int> dialled;
     do {
       // report which links survived, drop the rest
       std::vector<int> good;
@@ -162,10 +169,13 @@ bool HostComm::Connect(const char *cmd) {
         if (!nl.sock.Connect(utils::SockAddr(peer_host.c_str(), peer_port))) {
           nl.sock.Close(); ++nerr; continue;
         }
+        // handshake: who I am, whom I mean to reach (a stale address in the tracker's table can belong to a
+        // different worker by now: ephemeral ports are recycled quickly), and who answered
         int echoed = -1;
-        if (!nl.sock.SendInt(rank) || !nl.sock.RecvInt(&echoed) || echoed != peer_rank) {
+        if (!nl.sock.SendInt(rank) || !nl.sock.SendInt(peer_rank) || !nl.sock.RecvInt(&echoed) || echoed != peer_rank) {
           nl.sock.Close(); ++nerr; continue;
         }
+        dialled.push_back(peer_rank);
         nl.rank = peer_rank;
         Link *old = FindLink(peer_rank);
         if (old != nullptr) { old->sock.Close(); old->sock = nl.sock; } else { links_.push_back(nl); }
@@ -175,10 +185,27 @@ bool HostComm::Connect(const char *cmd) {
     utils::Check(t.SendInt(port), "tracker: cannot send port");
     t.Close();
 
-    for (int i = 0; i < naccept; ++i) {
+    // The tracker only says HOW MANY peers will dial us. A peer whose own rendezvous attempt failed half-way
+    // dials again on its retry, so count distinct ranks: a repeated rank replaces its older socket.
+    // Only neighbours we did not dial ourselves may connect, and only if they really meant us.
+    std::vector<int> expected(tree_nbrs);
+    if (ring_prev_rank >= 0) expected.push_back(ring_prev_rank);
+    if (ring_next_rank >= 0) expected.push_back(ring_next_rank);
+    std::vector<int> accepted;
+    while (static_cast<int>(accepted.size()) < naccept) {
       Link nl;
       nl.sock = listener.Accept();
-      utils::Check(nl.sock.SendInt(rank) && nl.sock.RecvInt(&nl.rank), "peer handshake failed");
+      int intended = -1;
+      if (!nl.sock.SendInt(rank) || !nl.sock.RecvInt(&nl.rank) || !nl.sock.RecvInt(&intended) || intended != rank ||
+          std::find(expected.begin(), expected.end(), nl.rank) == expected.end()) {
+        nl.sock.Close();  // dialler died, or was sent here by mistake
+        continue;
+      }
+      // A neighbour that restarted its own rendezvous dials again: its new socket replaces the old one below,
+      // but it does not count towards the peers we are still waiting for.
+      const bool known = std::find(dialled.begin(), dialled.end(), nl.rank) != dialled.end() ||
+                         std::find(accepted.begin(), accepted.end(), nl.rank) != accepted.end();
+      if (!known) accepted.push_back(nl.rank);
       Link *old = FindLink(nl.rank);
       if (old != nullptr) { old->sock.Close(); old->sock = nl.sock; } else { links_.push_back(nl); }
     }
@@ -205,6 +232,10 @@ bool HostComm::Connect(const char *cmd) {
     return true;
   } catch (const std::exception &e) {
     fprintf(stderr, "[rabit] rendezvous (%s) failed: %s\n", cmd, e.what());
+    // leave nothing half-built behind: the caller retries from scratch
+    for (Link &l : links_) l.sock.Close();
+    links_.clear();
+    tree_.clear(); parent_slot_ = -1; ring_prev_ = ring_next_ = nullptr;
     return false;
   }
 }
@@ -269,7 +300,12 @@ Status HostComm::AllreduceTree(void *buf_, size_t eb, size_t count, ReduceFuncti
       if (sent_up < reduced) poll.WatchWrite(parent->sock.fd);
       if (recv_down < sent_up) poll.WatchRead(parent->sock.fd);
     }
-    poll.Poll();
+    // a neighbour this primitive does not talk to may have died: nothing would ever wake us up, so probe
+    // all links whenever nothing moved for a while
+    if (poll.Poll(kProbeMs) == 0) {
+      if (LinksBroken()) return Status::kPeerClosed;
+      continue;
+    }
     // up: children -> staging
     for (Child &c : kids) {
       if (c.recvd < total && c.recvd - reduced < cap && poll.CheckRead(c.l->sock.fd)) {
@@ -338,7 +374,12 @@ Status HostComm::Broadcast(void *buf_, size_t size, int root) {
       if (upstream == -1 || (i == upstream && recvd < size)) poll.WatchRead(fd);
       if (upstream != -1 && i != upstream && sent[i] < recvd) poll.WatchWrite(fd);
     }
-    poll.Poll();
+    // a neighbour this primitive does not talk to may have died: nothing would ever wake us up, so probe
+    // all links whenever nothing moved for a while
+    if (poll.Poll(kProbeMs) == 0) {
+      if (LinksBroken()) return Status::kPeerClosed;
+      continue;
+    }
     if (upstream == -1) {
       for (int i = 0; i < nl && upstream == -1; ++i) {
         if (!poll.CheckRead(tree_[i]->sock.fd)) continue;
@@ -382,7 +423,12 @@ Status HostComm::AllgatherRing(void *buf_, size_t total, size_t slice_begin, siz
     poll.Clear();
     if (recvd < total_recv) poll.WatchRead(ring_next_->sock.fd);
     if (sent < sendable) poll.WatchWrite(ring_prev_->sock.fd);
-    poll.Poll();
+    // a neighbour this primitive does not talk to may have died: nothing would ever wake us up, so probe
+    // all links whenever nothing moved for a while
+    if (poll.Poll(kProbeMs) == 0) {
+      if (LinksBroken()) return Status::kPeerClosed;
+      continue;
+    }
     if (recvd < total_recv && poll.CheckRead(ring_next_->sock.fd)) {
       const size_t pos = (slice_end + recvd) % total;
       size_t got; Status s = RecvSome(ring_next_, buf + pos, std::min(total_recv - recvd, total - pos), &got);
@@ -427,7 +473,12 @@ Status HostComm::ReduceScatterRing(void *buf_, size_t eb, size_t count, ReduceFu
     const bool can_read = recvd < total_recv && recvd - reduced < cap;
     if (can_read) poll.WatchRead(ring_next_->sock.fd);
     if (sent < sendable) poll.WatchWrite(ring_prev_->sock.fd);
-    poll.Poll();
+    // a neighbour this primitive does not talk to may have died: nothing would ever wake us up, so probe
+    // all links whenever nothing moved for a while
+    if (poll.Poll(kProbeMs) == 0) {
+      if (LinksBroken()) return Status::kPeerClosed;
+      continue;
+    }
     if (can_read && poll.CheckRead(ring_next_->sock.fd)) {
       const size_t off = recvd % cap;
       size_t want = std::min(total_recv - recvd, cap - (recvd - reduced));
@@ -477,7 +528,12 @@ Status HostComm::RelayImpl(Link *from, Link *to, void *buf_, size_t size) {
     poll.Clear();
     if (recvd < size) poll.WatchRead(from->sock.fd);
     if (sent < recvd) poll.WatchWrite(to->sock.fd);
-    poll.Poll();
+    // a neighbour this primitive does not talk to may have died: nothing would ever wake us up, so probe
+    // all links whenever nothing moved for a while
+    if (poll.Poll(kProbeMs) == 0) {
+      if (LinksBroken()) return Status::kPeerClosed;
+      continue;
+    }
     if (recvd < size && poll.CheckRead(from->sock.fd)) {
       size_t got; Status s = RecvSome(from, buf + recvd, size - recvd, &got);
       if (!Ok(s)) return s;
@@ -517,7 +573,12 @@ Status HostComm::RingShift(const void *send_, size_t nsend, void *recv_, size_t 
     poll.Clear();
     if (recvd < nrecv) poll.WatchRead(from->sock.fd);
     if (sent < nsend) poll.WatchWrite(to->sock.fd);
-    poll.Poll();
+    // a neighbour this primitive does not talk to may have died: nothing would ever wake us up, so probe
+    // all links whenever nothing moved for a while
+    if (poll.Poll(kProbeMs) == 0) {
+      if (LinksBroken()) return Status::kPeerClosed;
+      continue;
+    }
     if (recvd < nrecv && poll.CheckRead(from->sock.fd)) {
       size_t got; Status s = RecvSome(from, recv + recvd, nrecv - recvd, &got);
       if (!Ok(s)) return s;

@@ -65,7 +65,7 @@ class HostComm {
   /*! \brief talk to the tracker with cmd "start" or "recover" and (re)build every link */
   bool Connect(const char *cmd);
   /*! \brief drop every peer connection (peers see it as our failure and follow suit) */
-  void CloseLinks();
+  void CloseLinks(bool graceful = false);
   /*!
    * \brief non-blocking health probe of every peer link: true if any peer closed or reset its
    *  end. The device backend calls this while a kernel is spinning on a peer's flag, so that a

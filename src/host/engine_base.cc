@@ -59,7 +59,7 @@ bool BaseEngine::Init(int argc, char *argv[]) {
 
 bool BaseEngine::Shutdown(void) {
   if (device_) { device_->Detach(); device_.reset(); }
-  comm_.CloseLinks();
+  comm_.CloseLinks(true);
   comm_.SendShutdown();
   initialized_ = false;
   return true;
