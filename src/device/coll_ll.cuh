@@ -1,5 +1,5 @@
 /*!
- * rabit-b200: low-latency allreduce for tiny messages (<= kLLMaxBytes per rank).
+ * rabit-b200: low-latency allreduce for small messages (<= kLLMaxBytes = 32 KiB per rank).
  *
  * The one-shot kernel needs a flag barrier (release fences + a round trip) after staging. For a
  * few hundred bytes that barrier IS the cost. Here data and flag travel in the same 8-byte word:
@@ -23,7 +23,7 @@
 namespace rabit {
 namespace device {
 
-constexpr size_t kLLMaxBytes = 4096;                                   // payload per rank
+constexpr size_t kLLMaxBytes = 32768;                                  // payload per rank
 constexpr size_t kLLSlotWords = kLLMaxBytes / 4 + 2;                   // + the consensus word (padded)
 constexpr size_t kLLSlotBytes = kLLSlotWords * 8;                      // every word carries a tag
 constexpr size_t kLLBytes = 2 * kMaxRanks * kLLSlotBytes;              // two parities x one slot per source rank
@@ -71,12 +71,16 @@ __device__ __forceinline__ void OneShotLLBody(const Params &p) {
   const unsigned int units = words / kUnitWords;
   if (threadIdx.x == 0) s_verdict = kStOk;
   __syncthreads();
+  // the grid splits the units evenly; block b of every rank works on the same range
+  const unsigned int per_block = (units + gridDim.x - 1) / gridDim.x;
+  const unsigned int u_begin = blockIdx.x * per_block;
+  const unsigned int u_end = u_begin + per_block < units ? u_begin + per_block : units;
   // push: my words into slot `me` of every rank (own copy included, so that the reduce below is uniform)
-  for (unsigned int w = threadIdx.x; w < words; w += blockDim.x) {
+  for (unsigned int w = u_begin * kUnitWords + threadIdx.x; w < u_end * kUnitWords; w += blockDim.x) {
     const unsigned int v = user[w];
     for (int q = 0; q < n; ++q) StoreTagged(LLSlot(p, q, me) + w, v, tag);
   }
-  if (threadIdx.x < n) StoreTagged(LLSlot(p, threadIdx.x, me) + words, p.code[ix], tag);
+  if (blockIdx.x == 0 && threadIdx.x < n) StoreTagged(LLSlot(p, threadIdx.x, me) + words, p.code[ix], tag);
   // consensus: everybody must be asking for the same thing
   int verdict = kStOk;
   if (threadIdx.x < n) {
@@ -89,7 +93,7 @@ __device__ __forceinline__ void OneShotLLBody(const Params &p) {
   __syncthreads();
   if (s_verdict != kStOk) { Report(p, me, s_verdict); return; }
   // pull + reduce in rank order (identical on every rank => bit-identical results)
-  for (unsigned int u = threadIdx.x; u < units; u += blockDim.x) {
+  for (unsigned int u = u_begin + threadIdx.x; u < u_end; u += blockDim.x) {
     unsigned int acc[kUnitWords], in[kUnitWords];
     bool ok = true;
     for (int q = 0; q < n && ok; ++q) {

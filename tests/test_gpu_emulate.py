@@ -179,10 +179,10 @@ def test_library_kernels_were_launched():
 @pytest.mark.parametrize("op", [0, 1, 2, 3])
 @pytest.mark.parametrize("n", [2, 8])
 def test_low_latency_tagged_word_allreduce(dtype, op, n):
-    """algo 9: data and flag travel in the same 8-byte word, no barrier (<= 4 KiB per rank)"""
+    """algo 9: data and flag travel in the same 8-byte word, no barrier (<= 32 KiB per rank)"""
     if op == 3 and dtype.is_floating_point:
         pytest.skip("BitOR is undefined on floating point")
-    for nbytes in (8, 40, 4096):
+    for nbytes in (8, 40, 4096, 12296, 32768):
         count = nbytes // torch.empty((), dtype=dtype).element_size()
         bufs = _inputs(n, count, dtype, seed=nbytes + op)
         keeps = [torch.zeros_like(b) for b in bufs]
