@@ -224,7 +224,7 @@ class RobustEngine : public BaseEngine {
    *  now execute the step itself.
    */
   bool Consensus(void *buf, size_t size, uint32_t flags, uint32_t seq,
-                 const std::function<void *()> *lazy_buf = nullptr);
+                 const std::function<void *()> *lazy_buf = nullptr, proto::InlineOp *inline_op = nullptr);
   /*! \brief failure handler: kOk -> true; otherwise tear down, re-rendezvous, return false */
   bool Healthy(Status s);
   void StartWatchdog();

@@ -96,7 +96,11 @@ void RobustEngine::RunOp(OpArgs *a) {
       if (st != Status::kMismatch) Healthy(st);
     }
     const std::function<void *()> lazy = [&]() -> void * { need_view(); return view; };
-    recovered = Consensus(view, a->bytes, flags, static_cast<uint32_t>(seq_), &lazy);
+    // tiny host allreduces without a lazy prepare ride along with the consensus round itself
+    proto::InlineOp inl{view, a->elem_bytes, a->count, a->reducer, false};
+    const bool can_inline = a->kind == OpKind::kAllreduce && !on_device && a->prepare_fun == nullptr &&
+                            a->bytes != 0 && a->bytes <= proto::kInlineBytes;
+    recovered = Consensus(view, a->bytes, flags, static_cast<uint32_t>(seq_), &lazy, can_inline ? &inl : nullptr);
     if (boot && recovered) {
       // the cache was just restored from a peer: this op must be in it
       utils::Check(BootLookup(a->key, view, a->bytes),
@@ -112,6 +116,12 @@ void RobustEngine::RunOp(OpArgs *a) {
       break;
     }
     in_sync_ = true;  // the consensus round just said: every rank is about to run this very op
+    if (inl.done) {
+      // the result came back with the consensus round: cache it like any other
+      slot = results_.AllocTemp(a->bytes);
+      std::memcpy(slot, view, a->bytes);
+      break;
+    }
     if (use_kernel) continue;
     need_view();
     prepare_once();

@@ -122,17 +122,56 @@ bool RobustEngine::Healthy(Status s) {
 }
 
 // ----------------------------------------------------------------- consensus
+namespace {
+thread_local proto::InlineOp *tl_inline = nullptr;  // reducer context while the envelope allreduce runs
+
+void EnvelopeReduce(const void *src_, void *dst_, int count, const MPI::Datatype &) {
+  const proto::Envelope *src = static_cast<const proto::Envelope *>(src_);
+  proto::Envelope *dst = static_cast<proto::Envelope *>(dst_);
+  for (int i = 0; i < count; ++i) {
+    dst[i].sum.Merge(src[i].sum);
+    const bool same_op = src[i].state == 1 && dst[i].state == 1 && src[i].signature == dst[i].signature &&
+                         src[i].bytes == dst[i].bytes;
+    proto::InlineOp *op = tl_inline;
+    if (same_op && op != nullptr && op->item_bytes * op->count == dst[i].bytes) {
+      op->reducer(src[i].payload, dst[i].payload, static_cast<int>(op->count), MPI::Datatype(op->item_bytes));
+    } else {
+      dst[i].state = 2;  // somebody is elsewhere in the program: whatever is in the payload is meaningless
+    }
+  }
+}
+}  // namespace
+
 bool RobustEngine::Consensus(void *buf, size_t size, uint32_t flags, uint32_t seq,
-                             const std::function<void *()> *lazy_buf) {
+                             const std::function<void *()> *lazy_buf, proto::InlineOp *inline_op) {
   Request me{seq, flags, static_cast<uint32_t>(boot_cache_.size())};
+  std::unique_ptr<proto::Envelope> env(new proto::Envelope());
   while (true) {
     this->ReportStatus();
     me.cache_count = static_cast<uint32_t>(boot_cache_.size());
-    Summary sum = Summary::Of(me);
-    if (!Healthy(comm_.Allreduce(&sum, sizeof(sum), 1, proto::SummaryReduce))) continue;
+    std::memset(env.get(), 0, sizeof(proto::Envelope));
+    env->sum = Summary::Of(me);
+    if (inline_op != nullptr) {
+      env->state = 1;
+      env->bytes = static_cast<uint32_t>(inline_op->item_bytes * inline_op->count);
+      env->signature = (seq * 2654435761u) ^ (static_cast<uint32_t>(inline_op->item_bytes) << 20) ^
+                       static_cast<uint32_t>(inline_op->count);
+      std::memcpy(env->payload, inline_op->data, env->bytes);
+    }
+    tl_inline = inline_op;
+    const Status st = comm_.AllreduceTree(env.get(), sizeof(proto::Envelope), 1, EnvelopeReduce);
+    tl_inline = nullptr;
+    if (!Healthy(st)) continue;
+    const Summary sum = env->sum;
     const proto::Verdict v = proto::Decide(sum, me);
     switch (v.action) {
-      case proto::kExecute: return false;
+      case proto::kExecute:
+        if (inline_op != nullptr && env->state == 1) {
+          // every rank shipped this very operation: the reduced payload IS the result
+          std::memcpy(inline_op->data, env->payload, env->bytes);
+          inline_op->done = true;
+        }
+        return false;
       case proto::kDone: return true;
       case proto::kRetry: break;
       case proto::kServeLoad:

@@ -77,6 +77,30 @@ inline void SummaryReduce(const void *src_, void *dst_, int count, const MPI::Da
   for (int i = 0; i < count; ++i) dst[i].Merge(src[i]);
 }
 
+/*!
+ * \brief what actually travels in a consensus round: the summary plus, for tiny allreduces, the payload
+ *  itself. If the verdict is "execute now" and every rank shipped the same operation, the reduced payload
+ *  is already the result and the separate payload collective is skipped — one network round trip per
+ *  small allreduce instead of the reference's two (allreduce_robust.cc:267 then :282).
+ *  Every rank sends an Envelope in every round (fixed size), whatever it is doing.
+ */
+const uint32_t kInlineBytes = 1024;
+struct Envelope {
+  Summary sum;
+  uint32_t state;      // 0 no payload, 1 payload valid so far, 2 poisoned (ranks disagree on the operation)
+  uint32_t signature;  // identifies the operation: hash of (seq, item size, item count)
+  uint32_t bytes;
+  uint32_t reserved;
+  unsigned char payload[kInlineBytes];
+};
+/*! \brief reducer context of the rank running the envelope allreduce (thread local, set by Consensus) */
+struct InlineOp {
+  void *data;                // in: this rank's contribution, out: the result when done
+  size_t item_bytes, count;
+  void (*reducer)(const void *src, void *dst, int count, const MPI::Datatype &dtype);
+  bool done;
+};
+
 enum Action {
   kExecute = 0,     // nobody is behind: run the requested step now
   kDone = 1,        // the request is satisfied (barrier passed / data recovered)
