@@ -5,8 +5,9 @@
  * Role parity with reference src/allreduce_base.{h,cc} (tracker handshake 221-438, tree
  * allreduce 476-668, flood broadcast 677-765, ring allgather 779-843, ring reduce-scatter
  * 857-946). The structure is different on purpose: every primitive is a small byte-flow
- * state machine driven by one shared poll loop (`Pump`), and recovery payloads move with
- * `RingRelay` along the rank ring instead of being routed over the tree.
+ * state machine over non-blocking sockets (byte counters + one poll loop each, with an idle probe
+ * for neighbours that died silently), and recovery payloads move with `RingRelay` along the rank
+ * ring instead of being routed over the tree.
  *
  * Every Try-style call returns a Status instead of throwing: a lost peer is a normal
  * event that the robust engine turns into "close everything, re-rendezvous, re-decide".

@@ -97,9 +97,10 @@ void RobustEngine::RunOp(OpArgs *a) {
     }
     const std::function<void *()> lazy = [&]() -> void * { need_view(); return view; };
     // tiny host allreduces without a lazy prepare ride along with the consensus round itself
-    proto::InlineOp inl{view, a->elem_bytes, a->count, a->reducer, false};
-    const bool can_inline = a->kind == OpKind::kAllreduce && !on_device && a->prepare_fun == nullptr &&
-                            a->bytes != 0 && a->bytes <= proto::kInlineBytes;
+    proto::InlineOp inl{view, a->elem_bytes, a->count, -1, a->reducer, false};
+    if (a->kind == OpKind::kBroadcast) { inl.item_bytes = 1; inl.count = a->bytes; inl.bcast_root = a->root; }
+    const bool can_inline = (a->kind == OpKind::kAllreduce || a->kind == OpKind::kBroadcast) && !on_device &&
+                            a->prepare_fun == nullptr && a->bytes != 0 && a->bytes <= proto::kInlineBytes;
     recovered = Consensus(view, a->bytes, flags, static_cast<uint32_t>(seq_), &lazy, can_inline ? &inl : nullptr);
     if (boot && recovered) {
       // the cache was just restored from a peer: this op must be in it

@@ -130,11 +130,15 @@ void EnvelopeReduce(const void *src_, void *dst_, int count, const MPI::Datatype
   proto::Envelope *dst = static_cast<proto::Envelope *>(dst_);
   for (int i = 0; i < count; ++i) {
     dst[i].sum.Merge(src[i].sum);
-    const bool same_op = src[i].state == 1 && dst[i].state == 1 && src[i].signature == dst[i].signature &&
-                         src[i].bytes == dst[i].bytes;
+    const bool same_sig = src[i].signature == dst[i].signature && src[i].bytes == dst[i].bytes;
+    const uint32_t a = src[i].state, b = dst[i].state;
     proto::InlineOp *op = tl_inline;
-    if (same_op && op != nullptr && op->item_bytes * op->count == dst[i].bytes) {
+    if (a == 1 && b == 1 && same_sig && op != nullptr && op->bcast_root < 0 &&
+        op->item_bytes * op->count == dst[i].bytes) {
       op->reducer(src[i].payload, dst[i].payload, static_cast<int>(op->count), MPI::Datatype(op->item_bytes));
+    } else if (same_sig && ((a == 4 && b == 3) || (a == 3 && b == 4) || (a == 3 && b == 3))) {
+      // broadcast: the root's bytes win over the receivers' empty payloads
+      if (a == 4) { std::memcpy(dst[i].payload, src[i].payload, src[i].bytes); dst[i].state = 4; }
     } else {
       dst[i].state = 2;  // somebody is elsewhere in the program: whatever is in the payload is meaningless
     }
@@ -152,11 +156,12 @@ bool RobustEngine::Consensus(void *buf, size_t size, uint32_t flags, uint32_t se
     std::memset(env.get(), 0, sizeof(proto::Envelope));
     env->sum = Summary::Of(me);
     if (inline_op != nullptr) {
-      env->state = 1;
+      const bool bcast = inline_op->bcast_root >= 0;
+      env->state = !bcast ? 1 : (inline_op->bcast_root == comm_.rank ? 4 : 3);
       env->bytes = static_cast<uint32_t>(inline_op->item_bytes * inline_op->count);
       env->signature = (seq * 2654435761u) ^ (static_cast<uint32_t>(inline_op->item_bytes) << 20) ^
-                       static_cast<uint32_t>(inline_op->count);
-      std::memcpy(env->payload, inline_op->data, env->bytes);
+                       static_cast<uint32_t>(inline_op->count) ^ (bcast ? 0x80000000u + inline_op->bcast_root : 0u);
+      if (env->state != 3) std::memcpy(env->payload, inline_op->data, env->bytes);
     }
     tl_inline = inline_op;
     const Status st = comm_.AllreduceTree(env.get(), sizeof(proto::Envelope), 1, EnvelopeReduce);
@@ -166,7 +171,7 @@ bool RobustEngine::Consensus(void *buf, size_t size, uint32_t flags, uint32_t se
     const proto::Verdict v = proto::Decide(sum, me);
     switch (v.action) {
       case proto::kExecute:
-        if (inline_op != nullptr && env->state == 1) {
+        if (inline_op != nullptr && env->state == (inline_op->bcast_root >= 0 ? 4u : 1u)) {
           // every rank shipped this very operation: the reduced payload IS the result
           std::memcpy(inline_op->data, env->payload, env->bytes);
           inline_op->done = true;

@@ -87,7 +87,8 @@ inline void SummaryReduce(const void *src_, void *dst_, int count, const MPI::Da
 const uint32_t kInlineBytes = 1024;
 struct Envelope {
   Summary sum;
-  uint32_t state;      // 0 no payload, 1 payload valid so far, 2 poisoned (ranks disagree on the operation)
+  uint32_t state;      // 0 no payload, 1 allreduce payload valid so far, 2 poisoned (ranks disagree on the
+                       // operation), 3 broadcast receiver, 4 broadcast payload (from the root)
   uint32_t signature;  // identifies the operation: hash of (seq, item size, item count)
   uint32_t bytes;
   uint32_t reserved;
@@ -96,7 +97,8 @@ struct Envelope {
 /*! \brief reducer context of the rank running the envelope allreduce (thread local, set by Consensus) */
 struct InlineOp {
   void *data;                // in: this rank's contribution, out: the result when done
-  size_t item_bytes, count;
+  size_t item_bytes, count;  // broadcast: item_bytes = 1, count = size
+  int bcast_root;            // -1: allreduce; otherwise broadcast from this rank
   void (*reducer)(const void *src, void *dst, int count, const MPI::Datatype &dtype);
   bool done;
 };
