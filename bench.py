@@ -109,6 +109,22 @@ class ClockSampler(object):
         return out
 
 
+def ensure_built(rank):
+    """lib/librabit.so normally travels with the snapshot; build it (rank 0 only) if it is missing."""
+    lib = os.path.join(ROOT, "lib", "librabit.so")
+    if os.path.isfile(lib):
+        return
+    if rank == 0:
+        import build as _build
+        _build.build(cuda=True, verbose=False)
+    else:
+        for _ in range(1800):
+            if os.path.isfile(lib):
+                time.sleep(2.0)
+                return
+            time.sleep(1.0)
+
+
 def make_store(rank, world):
     """torchrun's MASTER_ADDR/PORT rendezvous as a key-value store (also used to share the tracker port)."""
     import datetime
@@ -140,6 +156,7 @@ def run_ours(args):
     import numpy as np
     import torch
     rank, world, local = dist_env()
+    ensure_built(rank)
     assert world == args.gpus or world == 1, "launch with torchrun --nproc-per-node == --gpus"
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
