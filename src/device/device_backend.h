@@ -37,6 +37,12 @@ class DeviceBackend {
   /*! \brief does ptr point into CUDA device memory? (false without CUDA) */
   static bool IsDevicePointer(const void *ptr);
   static bool Compiled();
+  /*!
+   * \brief plain cudaMemcpy between a device pointer and host memory, usable WITHOUT a backend instance:
+   *  the engines stage device buffers through the host TCP collectives when no arena could be attached
+   *  (ranks on different hosts, more than one NVLink domain, rabit_device=off). to_device: host -> device.
+   */
+  static void RawCopy(void *dst, const void *src, size_t nbytes, bool to_device);
 
   /*!
    * \brief (re)build the symmetric arena: allocate if needed, exchange handles with all

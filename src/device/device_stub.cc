@@ -9,6 +9,7 @@ namespace engine {
 DeviceBackend *DeviceBackend::Create(const Config &) { return nullptr; }
 bool DeviceBackend::IsDevicePointer(const void *) { return false; }
 bool DeviceBackend::Compiled() { return false; }
+void DeviceBackend::RawCopy(void *, const void *, size_t, bool) {}
 class BaseEngine;
 BaseEngine *CreateNcclEngine() { return nullptr; }
 }  // namespace engine

@@ -77,18 +77,17 @@ void BaseEngine::AllreduceTyped(void *buf, size_t type_nbytes, size_t count, Red
   if (prepare_fun != nullptr) prepare_fun(prepare_arg);
   if (comm_.world <= 1 && !(device_ && comm_.cfg.device_force)) return;
   if (Classify(buf) == MemKind::kDevice) {
-    utils::Check(device_ != nullptr, "Allreduce on a device pointer but the device backend is not available");
-    if (dtype >= 0 && op >= 0) {
+    if (device_ != nullptr && dtype >= 0 && op >= 0) {
       Status s = device_->Allreduce(buf, count, dtype, op, 1, 0, nullptr);
       if (!Ok(s)) Fatal(s, "device allreduce");
       return;
     }
-    // opaque reducer: stage through the host
+    // opaque reducer, or no arena attached (several hosts, rabit_device=off): stage through the host
     std::string tmp(type_nbytes * count, '\0');
-    device_->CopyD2H(&tmp[0], buf, tmp.size());
+    DeviceBackend::RawCopy(&tmp[0], buf, tmp.size(), false);
     Status s = comm_.Allreduce(&tmp[0], type_nbytes, count, reducer);
     if (!Ok(s)) Fatal(s, "allreduce");
-    device_->CopyH2D(buf, tmp.data(), tmp.size());
+    DeviceBackend::RawCopy(buf, tmp.data(), tmp.size(), true);
     return;
   }
   Status s = comm_.Allreduce(buf, type_nbytes, count, reducer);
@@ -99,9 +98,16 @@ void BaseEngine::AllreduceTyped(void *buf, size_t type_nbytes, size_t count, Red
 void BaseEngine::Broadcast(void *buf, size_t size, int root, const char *, const int, const char *) {
   if (comm_.world <= 1) return;
   if (Classify(buf) == MemKind::kDevice) {
-    utils::Check(device_ != nullptr, "Broadcast on a device pointer but the device backend is not available");
-    Status s = device_->Broadcast(buf, size, root, 0, nullptr);
-    if (!Ok(s)) Fatal(s, "device broadcast");
+    if (device_ != nullptr) {
+      Status s = device_->Broadcast(buf, size, root, 0, nullptr);
+      if (!Ok(s)) Fatal(s, "device broadcast");
+      return;
+    }
+    std::string tmp(size, '\0');
+    if (comm_.rank == root) DeviceBackend::RawCopy(&tmp[0], buf, size, false);
+    Status s = comm_.Broadcast(&tmp[0], size, root);
+    if (!Ok(s)) Fatal(s, "broadcast");
+    if (comm_.rank != root) DeviceBackend::RawCopy(buf, tmp.data(), size, true);
     return;
   }
   Status s = comm_.Broadcast(buf, size, root);
@@ -113,9 +119,16 @@ void BaseEngine::Allgather(void *buf, size_t total_size, size_t slice_begin, siz
                            size_t size_prev_slice, const char *, const int, const char *) {
   if (comm_.world <= 1) return;
   if (Classify(buf) == MemKind::kDevice) {
-    utils::Check(device_ != nullptr, "Allgather on a device pointer but the device backend is not available");
-    Status s = device_->Allgather(buf, total_size, slice_begin, slice_end, 0, nullptr);
-    if (!Ok(s)) Fatal(s, "device allgather");
+    if (device_ != nullptr) {
+      Status s = device_->Allgather(buf, total_size, slice_begin, slice_end, 0, nullptr);
+      if (!Ok(s)) Fatal(s, "device allgather");
+      return;
+    }
+    std::string tmp(total_size, '\0');
+    DeviceBackend::RawCopy(&tmp[slice_begin], static_cast<char *>(buf) + slice_begin, slice_end - slice_begin, false);
+    Status s = comm_.AllgatherRing(&tmp[0], total_size, slice_begin, slice_end, size_prev_slice);
+    if (!Ok(s)) Fatal(s, "allgather");
+    DeviceBackend::RawCopy(buf, tmp.data(), total_size, true);
     return;
   }
   Status s = comm_.AllgatherRing(buf, total_size, slice_begin, slice_end, size_prev_slice);

@@ -34,15 +34,21 @@ void RobustEngine::RunOp(OpArgs *a) {
     if (a->prepare_fun != nullptr) a->prepare_fun(a->prepare_arg);
     return;
   }
-  utils::Check(!on_device || device_ != nullptr,
-               "collective on a CUDA device pointer, but the device backend is unavailable "
-               "(library built without nvcc, no GPU, or rabit_device=off)");
+  // A device pointer without an attached arena (ranks on several hosts, rabit_device=off, no P2P) still
+  // works: the bytes are staged through the host collectives below, recovery semantics unchanged.
+  auto to_device = [&](void *dst, const void *src, size_t n) {
+    if (device_) device_->CopyH2D(dst, src, n); else DeviceBackend::RawCopy(dst, src, n, true);
+  };
+  auto to_host = [&](void *dst, const void *src, size_t n) {
+    if (device_) device_->CopyD2H(dst, src, n); else DeviceBackend::RawCopy(dst, src, n, false);
+  };
   const double t0 = utils::GetTime();
   const bool boot = comm_.cfg.bootstrap_cache && !checkpoint_loaded_;
   const uint32_t flags = boot ? proto::kLoadCache : 0;
 
   // device buffers whose op the kernels cannot express go through a host mirror
-  const bool fused = on_device && (a->kind != OpKind::kAllreduce || (a->dtype >= 0 && a->op >= 0));
+  const bool fused = on_device && device_ != nullptr &&
+                     (a->kind != OpKind::kAllreduce || (a->dtype >= 0 && a->op >= 0));
   // (allocated only when the host protocol actually has to look at the bytes)
   std::string mirror;
   char *view = static_cast<char *>(a->buf);
@@ -59,7 +65,7 @@ void RobustEngine::RunOp(OpArgs *a) {
 
   if (boot) need_view();
   if (boot && BootLookup(a->key, view, a->bytes)) {
-    if (on_device) device_->CopyH2D(a->buf, view, a->bytes);
+    if (on_device) to_device(a->buf, view, a->bytes);
     return;
   }
 
@@ -106,14 +112,14 @@ void RobustEngine::RunOp(OpArgs *a) {
       // the cache was just restored from a peer: this op must be in it
       utils::Check(BootLookup(a->key, view, a->bytes),
                    "[%d] bootstrap collective %s is not in the restored cache", comm_.rank, a->key.c_str());
-      if (on_device) device_->CopyH2D(a->buf, view, a->bytes);
+      if (on_device) to_device(a->buf, view, a->bytes);
       return;
     }
     if (!dropped) { DropStaleResult(); dropped = true; }
     if (recovered) {
       slot = results_.AllocTemp(a->bytes);
       std::memcpy(slot, view, a->bytes);
-      if (on_device) device_->CopyH2D(a->buf, view, a->bytes);
+      if (on_device) to_device(a->buf, view, a->bytes);
       break;
     }
     in_sync_ = true;  // the consensus round just said: every rank is about to run this very op
@@ -127,13 +133,13 @@ void RobustEngine::RunOp(OpArgs *a) {
     need_view();
     prepare_once();
     slot = results_.AllocTemp(a->bytes);
-    if (on_device) device_->CopyD2H(view, a->buf, a->bytes);
+    if (on_device) to_host(view, a->buf, a->bytes);
     std::memcpy(slot, view, a->bytes);
     // the transfer works on the cache slot so that a failure half-way leaves the caller's buffer
     // intact for the retry
     if (Healthy(TryOp(*a, slot))) {
       std::memcpy(view, slot, a->bytes);
-      if (on_device) device_->CopyH2D(a->buf, view, a->bytes);
+      if (on_device) to_device(a->buf, view, a->bytes);
       break;
     }
   }
