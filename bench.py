@@ -363,6 +363,11 @@ def run_ours(args):
             "gpu_launches": int(launches),
             "clocks": clocks,
         }
+        if n == 1:
+            out["config"]["single_rank_note"] = (
+                "one rank: an allreduce is the identity and the reference returns without moving a byte; the timed kernel "
+                "still runs its publish / reduce / write-back passes over local HBM (no NVLink traffic), so this is an "
+                "HBM-bound figure of the kernel, not a communication figure; busbw is the metric to compare across N")
         if nccl_ms is not None:
             out["nccl"] = {"ms_per_step": nccl_ms, "busbw_GBps": S / (nccl_ms * 1e-3) / 1e9 * (2.0 * (n - 1) / n)}
         if sweep:
