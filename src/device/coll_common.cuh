@@ -49,6 +49,10 @@ struct Control {
   // start and the last block to finish bumps it (kept at the end: the offsets of the rows above never move)
   unsigned int epoch_dev;
   unsigned int done_count;
+  // commit gate of the fault-tolerant path: every block posts (epoch + 1) << 32 | verdict in its own slot,
+  // block 0 folds them and posts the grid's verdict in gate_go (no contended atomics)
+  unsigned long long gate_slot[kMaxBlocks];
+  unsigned long long gate_go;
 };
 static_assert(sizeof(Control) <= kCtrlBytes, "control block too small");
 
@@ -169,6 +173,72 @@ __device__ __forceinline__ void Report(const Params &p, int me, int verdict) {
   if (threadIdx.x == 0 && verdict != kStOk) {
     atomicCAS(p.status + (p.emulate ? me : 0), kStOk, verdict);
   }
+}
+
+/*!
+ * \brief all-or-nothing commit point of ONE rank's grid, used on the fault-tolerant path only (a result-cache
+ *  copy was requested). The flag barriers are per block channel, so when a peer dies in the middle of a kernel
+ *  some blocks of a survivor may pass their last barrier while others time out. An allreduce must then not
+ *  touch the caller's buffer at all: the engine retries the op from that buffer (the reference reduces inside
+ *  its cache slot for the same reason, allreduce_robust.cc:279-283). Every block arrives here with its own
+ *  verdict after the last barrier that guards the first write into the user buffer; blocks that passed wait
+ *  for the whole grid and proceed only if nobody failed. Failed blocks arrive and leave at once.
+ *  Local memory traffic only: every block posts its verdict in its own slot, block 0 folds them and posts the
+ *  grid's verdict (two L2 round trips, no contended atomics). Needs the grid co-resident, which the launch
+ *  configuration guarantees (<= one block per SM).
+ */
+__device__ __forceinline__ int CommitGate(const Params &p, int me, int verdict, int *s_verdict) {
+  if (p.keep[p.emulate ? me : 0] == nullptr || gridDim.x == 1) return verdict;
+  __syncthreads();
+  Control *c = CtrlOf(p, me);
+  const unsigned long long tag = static_cast<unsigned long long>(OpEpoch(p) + 1) << 32;
+  const int t = threadIdx.x;
+  if (t == 0) {
+    *s_verdict = verdict;
+    asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(&c->gate_slot[blockIdx.x]),
+                 "l"(tag | static_cast<unsigned long long>(verdict)) : "memory");
+  }
+  if (blockIdx.x != 0 && verdict != kStOk) return verdict;  // posted; nobody waits for a block that failed
+  __syncthreads();
+  const unsigned long long deadline = GlobalTimer() + p.timeout_ns;
+  unsigned int spins = 0;
+  if (blockIdx.x == 0) {
+    // coordinator: thread i watches block i (its own failure is published without waiting for anybody)
+    if (verdict == kStOk) {
+      for (unsigned int b = t; b < gridDim.x; b += blockDim.x) {
+        int seen = kStOk;
+        while (true) {
+          unsigned long long v;
+          asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(&c->gate_slot[b]) : "memory");
+          if ((v >> 32) == (tag >> 32)) { if (static_cast<unsigned int>(v) != 0u) seen = kStAborted; break; }
+          if ((++spins & 0x3ff) == 0) {
+            if (*p.abort_flag != 0) { seen = kStAborted; break; }
+            if (GlobalTimer() > deadline) { seen = kStTimeout; break; }
+          }
+        }
+        if (seen != kStOk) atomicMax(s_verdict, seen);
+      }
+    }
+    __syncthreads();
+    if (t == 0) {
+      asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(&c->gate_go),
+                   "l"(tag | static_cast<unsigned long long>(*s_verdict)) : "memory");
+    }
+  } else if (t == 0) {
+    int seen = kStOk;
+    while (true) {
+      unsigned long long v;
+      asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(&c->gate_go) : "memory");
+      if ((v >> 32) == (tag >> 32)) { if (static_cast<unsigned int>(v) != 0u) seen = kStAborted; break; }
+      if ((++spins & 0x3ff) == 0) {
+        if (*p.abort_flag != 0) { seen = kStAborted; break; }
+        if (GlobalTimer() > deadline) { seen = kStTimeout; break; }
+      }
+    }
+    *s_verdict = seen;
+  }
+  __syncthreads();
+  return *s_verdict;
 }
 
 /*! \brief first thing every kernel does: fetch the op epoch. All blocks read the same value because it is only

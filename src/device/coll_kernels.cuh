@@ -70,6 +70,7 @@ __device__ __forceinline__ void OneShotAllreduceBody(const Params &p) {
   CopyTiles<true>(user, StageOf(p, me), p.bytes, aligned);
   Stamp(p, 1);
   int verdict = FlagBarrier(p, me, EntryRow{OpEpoch(p) & 1u}, OpEpoch(p) + 1, p.code[p.emulate ? me : 0], true, &s_verdict);
+  verdict = CommitGate(p, me, verdict, &s_verdict);  // fault-tolerant path: all blocks or none
   if (verdict != kStOk) { Report(p, me, verdict); return; }
   Stamp(p, 2);
 
@@ -128,7 +129,7 @@ __device__ __forceinline__ void TwoShotAllreduceBody(const Params &p) {
   CopyTiles<true>(user, StageOf(p, me), p.bytes, aligned);
   Stamp(p, 1);
   int verdict = FlagBarrier(p, me, EntryRow{OpEpoch(p) & 1u}, OpEpoch(p) + 1, p.code[p.emulate ? me : 0], true, &s_verdict);
-  if (verdict != kStOk) { Report(p, me, verdict); return; }
+  if (verdict != kStOk) { CommitGate(p, me, verdict, &s_verdict); Report(p, me, verdict); return; }
   Stamp(p, 2);
 
   const size_t nvec_full = p.bytes / kVec;
@@ -169,6 +170,7 @@ __device__ __forceinline__ void TwoShotAllreduceBody(const Params &p) {
   }
   Stamp(p, 3);
   verdict = FlagBarrier(p, me, MidRow{}, OpEpoch(p) + 1, 0u, false, &s_verdict);
+  verdict = CommitGate(p, me, verdict, &s_verdict);  // fault-tolerant path: all blocks or none
   if (verdict != kStOk) { Report(p, me, verdict); return; }
   Stamp(p, 4);
   // allgather: pull every tile from its owner's stage

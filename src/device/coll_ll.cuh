@@ -91,10 +91,19 @@ __device__ __forceinline__ void OneShotLLBody(const Params &p) {
     if (verdict != kStOk) atomicMax(&s_verdict, verdict);
   }
   __syncthreads();
-  if (s_verdict != kStOk) { Report(p, me, s_verdict); return; }
-  // pull + reduce in rank order (identical on every rank => bit-identical results)
-  for (unsigned int u = u_begin + threadIdx.x; u < u_end; u += blockDim.x) {
-    unsigned int acc[kUnitWords], in[kUnitWords];
+  if (s_verdict != kStOk || per_block > blockDim.x) {
+    const int v = s_verdict != kStOk ? s_verdict : kStAborted;  // (a launch with too few threads is a host bug)
+    __syncthreads();
+    CommitGate(p, me, v, &s_verdict);
+    Report(p, me, v);
+    return;
+  }
+  // pull + reduce in rank order (identical on every rank => bit-identical results). The launch gives every
+  // thread at most ONE unit, so the result waits in registers until the whole grid is known to be complete.
+  const unsigned int u = u_begin + threadIdx.x;
+  const bool mine = u < u_end;
+  unsigned int acc[kUnitWords], in[kUnitWords];
+  if (mine) {
     bool ok = true;
     for (int q = 0; q < n && ok; ++q) {
       for (unsigned int k = 0; k < kUnitWords && ok; ++k) {
@@ -111,14 +120,19 @@ __device__ __forceinline__ void OneShotLLBody(const Params &p) {
         for (int l = 0; l < kLanes; ++l) a[l] = OP::Apply(a[l], b[l]);
       }
     }
-    if (!ok) { atomicMax(&s_verdict, verdict); break; }
+    if (!ok) atomicMax(&s_verdict, verdict);
+  }
+  __syncthreads();
+  verdict = s_verdict;
+  __syncthreads();  // s_verdict is about to be reused by the gate
+  verdict = CommitGate(p, me, verdict, &s_verdict);  // fault-tolerant path: all blocks or none
+  if (verdict != kStOk) { Report(p, me, verdict); return; }
+  if (mine) {
     for (unsigned int k = 0; k < kUnitWords; ++k) {
       user[u * kUnitWords + k] = acc[k];
       if (keep != nullptr) keep[u * kUnitWords + k] = acc[k];
     }
   }
-  __syncthreads();
-  if (s_verdict != kStOk) Report(p, me, s_verdict);
 }
 /*! \brief launch wrapper: epoch from the control block (BeginOp), body, completion count (EndOp) */
 template <typename T, typename OP>

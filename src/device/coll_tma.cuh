@@ -65,7 +65,7 @@ __device__ __forceinline__ void TwoShotAllreduceTmaBody(const Params &p, int dep
   CopyTiles<true>(user, StageOf(p, me), p.bytes, aligned);
   Stamp(p, 1);
   int verdict = FlagBarrier(p, me, EntryRow{OpEpoch(p) & 1u}, OpEpoch(p) + 1, p.code[p.emulate ? me : 0], true, &s_verdict);
-  if (verdict != kStOk) { Report(p, me, verdict); return; }
+  if (verdict != kStOk) { CommitGate(p, me, verdict, &s_verdict); Report(p, me, verdict); return; }
   Stamp(p, 2);
 
   const size_t nvec_full = p.bytes / kVec;
@@ -121,6 +121,7 @@ __device__ __forceinline__ void TwoShotAllreduceTmaBody(const Params &p, int dep
   }
   Stamp(p, 3);
   verdict = FlagBarrier(p, me, MidRow{}, OpEpoch(p) + 1, 0u, false, &s_verdict);
+  verdict = CommitGate(p, me, verdict, &s_verdict);  // fault-tolerant path: all blocks or none
   if (verdict != kStOk) { Report(p, me, verdict); return; }
   Stamp(p, 4);
   const size_t tile_vecs = static_cast<size_t>(blockDim.x) * kUnroll;

@@ -101,6 +101,14 @@ def main():
             rabit.allreduce(sx, rabit.MAX)
             want = torch.stack([contribution(sx.numel(), r, it, 103, dev) for r in range(world)]).max(0).values
             assert torch.equal(sx, want), "[%d] symmetric max mismatch iter %d" % (me, it)
+            if not any(a.startswith("mock=") for a in sys.argv):
+                # the async API reduces heap buffers in place (zero-copy kernels); it is not sequence-numbered,
+                # so it cannot be part of a run that replays iterations after a kill
+                sx.copy_(contribution(sx.numel(), me, it, 107, dev))
+                rt.allreduce_async_(sx)
+                rt.synchronize()
+                want = torch.stack([contribution(sx.numel(), r, it, 107, dev) for r in range(world)]).sum(0)
+                assert torch.equal(sx, want), "[%d] in-place async allreduce mismatch iter %d" % (me, it)
             if me == root:
                 sb.copy_(btruth[:sb.numel()])
             else:

@@ -70,10 +70,17 @@ def test_native_cpp_device_workload_with_kills(world):
 
 
 def test_device_symmetric_zero_copy_buffers(world):
-    """allreduce / broadcast on RabitDeviceSymAlloc buffers (in-place kernels), also across a kill"""
+    """allreduce / broadcast on RabitDeviceSymAlloc buffers through the fault-tolerant API, also across a kill"""
     res = _run(["100000", "rabit_device_heap=64M", "mock=1,1,3,0"], world, timeout=600)
     assert res.ok, {i: o[-2500:] for i, o in res.outputs.items()}
     assert res.restarts == 1
+
+
+def test_device_symmetric_async_in_place(world):
+    """heap buffers through the async API: reduced in place by the zero-copy kernels"""
+    res = _run(["100000", "rabit_device_heap=64M", "iters=2"], world, timeout=600)
+    assert res.ok, {i: o[-2500:] for i, o in res.outputs.items()}
+    assert res.restarts == 0
 
 
 def test_arena_grows_on_demand(world):
