@@ -74,6 +74,17 @@ class DeviceBackend {
   virtual void CopyH2D(void *dst, const void *src, size_t nbytes) = 0;
   virtual void CopyD2D(void *dst, const void *src, size_t nbytes) = 0;
 
+  // ---- copy engines next to the collective stream: host buffers that ride PCIe + NVLink in chunks ----
+  static const int kCopySlots = 4;
+  /*! \brief enqueue host -> device on the copy-in stream and remember its completion in `slot` */
+  virtual void PrefetchH2D(void *dst, const void *src, size_t nbytes, int slot) = 0;
+  /*! \brief the collective stream waits (on the device) for the copy remembered in `slot` */
+  virtual void AwaitPrefetch(int slot) = 0;
+  /*! \brief enqueue device -> host on the copy-out stream; the source must already be complete */
+  virtual void DrainD2H(void *dst, const void *src, size_t nbytes) = 0;
+  /*! \brief wait for everything enqueued by DrainD2H (and PrefetchH2D) */
+  virtual void DrainSync() = 0;
+
   virtual const DeviceStats &stats() const = 0;
   virtual std::string Describe() const = 0;
 };

@@ -66,6 +66,8 @@ struct Config {
   std::string device_algo = "auto";          // auto|oneshot|twoshot|tma|nvls
   bool device_force = false;                 // run kernels even at world size 1
   size_t device_cache_bytes = 16UL << 30;    // device-resident result cache budget
+  size_t device_host_min = 0;                // bytes: HOST buffers >= this ride PCIe + NVLink instead of TCP; 0 = off
+  size_t device_host_chunk = 16UL << 20;     // pipeline granule of that path (H2D | kernel | D2H overlap)
 
   /*! \brief names looked up in the environment at Init */
   static const std::vector<std::string> &EnvNames() {
@@ -78,6 +80,7 @@ struct Config {
       "rabit_engine", "rabit_device", "rabit_device_arena", "rabit_device_algo",
       "rabit_device_blocks", "rabit_device_timeout_ms", "rabit_device_force",
       "rabit_device_oneshot_max", "rabit_device_nvls_min", "rabit_device_pipe_min", "rabit_device_heap", "rabit_device_cache",
+      "rabit_device_host_min", "rabit_device_host_chunk",
       "rabit_world_size", "rabit_slave_port"};
     return names;
   }
@@ -142,6 +145,8 @@ struct Config {
     else if (is("rabit_device_pipe_min")) device_pipe_min = ParseBytes(name, val);
     else if (is("rabit_device_nvls_min")) device_nvls_min = ParseBytes(name, val);
     else if (is("rabit_device_cache")) device_cache_bytes = ParseBytes(name, val);
+    else if (is("rabit_device_host_min")) device_host_min = ParseBytes(name, val);
+    else if (is("rabit_device_host_chunk")) device_host_chunk = std::max<size_t>(ParseBytes(name, val), 64UL << 10);
     else if (is("rabit_device_blocks")) device_blocks = atoi(val);
     else if (is("rabit_device_timeout_ms")) device_timeout_ms = atoi(val);
     else if (is("rabit_device_algo")) device_algo = val;

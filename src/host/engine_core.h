@@ -216,6 +216,9 @@ class RobustEngine : public BaseEngine {
     std::string key;
   };
   void RunOp(OpArgs *a);
+  /*! \brief large host buffers: chunked H2D | device collective | D2H pipeline (engine_ops.cc); false = not taken */
+  bool HostViaDevice(void *buf, size_t type_nbytes, size_t count, ReduceFunction reducer, int dtype, int op,
+                     const std::string &key);
   Status TryOp(const OpArgs &a, char *slot);
 
   /*!

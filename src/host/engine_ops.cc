@@ -161,9 +161,58 @@ void RobustEngine::RunOp(OpArgs *a) {
   }
 }
 
+/*!
+ * A large HOST buffer rides PCIe + NVLink instead of the TCP links (no counterpart in the reference, whose
+ * only transport is the socket ring of allreduce_base.cc:857-977). The buffer is cut into chunks; every chunk
+ * is an ordinary sequence-numbered device-pointer op (fused kernel, result cached on the device, recoverable
+ * like any other), and the copies of neighbouring chunks overlap it: H2D(i+1..) | kernel(i) | D2H(i-1).
+ * A chunk's result is copied back only after its own op has succeeded, so after a failure the host buffer
+ * holds finished chunks and untouched inputs, never garbage; a restarted rank replays the same chunk ops.
+ * All ranks derive the same chunking from the same parameters.
+ */
+bool RobustEngine::HostViaDevice(void *buf, size_t type_nbytes, size_t count, ReduceFunction reducer, int dtype,
+                                 int op, const std::string &key) {
+  const size_t bytes = type_nbytes * count;
+  const Config &cfg = comm_.cfg;
+  if (device_ == nullptr || !device_->attached() || cfg.device_host_min == 0 || bytes < cfg.device_host_min) return false;
+  if (dtype < 0 || op < 0 || type_nbytes == 0) return false;
+  if (comm_.world <= 1 && !cfg.device_force) return false;
+  if (cfg.bootstrap_cache && !checkpoint_loaded_) return false;  // bootstrap ops are keyed by call site, not chunked
+  const size_t per_chunk = std::max<size_t>(cfg.device_host_chunk / type_nbytes, 1);
+  const size_t nchunk = (count + per_chunk - 1) / per_chunk;
+  char *host = static_cast<char *>(buf);
+  char *dev = static_cast<char *>(device_->Alloc(bytes));
+  const int depth = DeviceBackend::kCopySlots - 1;
+  auto begin = [&](size_t i) { return i * per_chunk * type_nbytes; };
+  auto span = [&](size_t i) { return std::min(per_chunk, count - i * per_chunk) * type_nbytes; };
+  for (size_t i = 0; i < nchunk && i < static_cast<size_t>(depth); ++i) {
+    device_->PrefetchH2D(dev + begin(i), host + begin(i), span(i), static_cast<int>(i));
+  }
+  for (size_t i = 0; i < nchunk; ++i) {
+    device_->AwaitPrefetch(static_cast<int>(i));
+    if (i + depth < nchunk) {
+      device_->PrefetchH2D(dev + begin(i + depth), host + begin(i + depth), span(i + depth), static_cast<int>(i + depth));
+    }
+    OpArgs a{};
+    a.kind = OpKind::kAllreduce; a.buf = dev + begin(i); a.bytes = span(i);
+    a.elem_bytes = type_nbytes; a.count = span(i) / type_nbytes; a.reducer = reducer; a.dtype = dtype; a.op = op;
+    a.key = key + "/" + std::to_string(i);
+    RunOp(&a);
+    device_->DrainD2H(host + begin(i), dev + begin(i), span(i));
+  }
+  device_->DrainSync();
+  device_->Free(dev);
+  return true;
+}
+
 void RobustEngine::AllreduceTyped(void *buf, size_t type_nbytes, size_t count, ReduceFunction reducer,
                                   int dtype, int op, PreprocFunction prepare_fun, void *prepare_arg,
                                   const char *_file, const int _line, const char *_caller) {
+  if (prepare_fun == nullptr && device_ != nullptr && comm_.cfg.device_host_min != 0 &&
+      Classify(buf) == MemKind::kHost &&
+      HostViaDevice(buf, type_nbytes, count, reducer, dtype, op, std::string(_file) + "::" + std::to_string(_line))) {
+    return;
+  }
   OpArgs a{};
   a.kind = OpKind::kAllreduce; a.buf = buf; a.bytes = type_nbytes * count;
   a.elem_bytes = type_nbytes; a.count = count; a.reducer = reducer; a.dtype = dtype; a.op = op;

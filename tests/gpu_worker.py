@@ -115,6 +115,20 @@ def main():
                 sb.zero_()
             rt.broadcast_(sb, root)
             assert torch.equal(sb, btruth[:sb.numel()]), "[%d] symmetric broadcast mismatch iter %d" % (me, it)
+        if any(a == "hostpipe=1" for a in sys.argv):
+            # large HOST buffers ride PCIe + NVLink in chunks (rabit_device_host_min): pageable numpy and pinned torch
+            hn = 3 * (1 << 20) + 17
+            base = (np.arange(hn, dtype=np.int64) % 61).astype(np.float32)
+            out = rabit.allreduce(base * (me + 1) + it, rabit.SUM)
+            want_h = base * (world * (world + 1) // 2) + it * world
+            assert np.array_equal(out, want_h), "[%d] host-pipe numpy allreduce mismatch iter %d" % (me, it)
+            pinned = torch.from_numpy(base * (me + 2)).pin_memory()
+            rt.allreduce_(pinned, rabit.MAX)
+            assert np.array_equal(pinned.numpy(), base * (world + 1)), "[%d] host-pipe pinned max mismatch" % me
+            hd = (np.arange(2 * 300000, dtype=np.int64) % 53).astype(np.float64) + me
+            out = rabit.allreduce(hd, rabit.SUM)
+            want_d = (np.arange(2 * 300000, dtype=np.int64) % 53).astype(np.float64) * world + world * (world - 1) / 2
+            assert np.array_equal(out, want_d), "[%d] host-pipe f64 allreduce mismatch iter %d" % (me, it)
         if graph:
             # capture three small collectives once, replay them several times on every rank
             gx = torch.zeros(2048, device=dev)

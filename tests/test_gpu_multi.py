@@ -83,6 +83,15 @@ def test_device_symmetric_async_in_place(world):
     assert res.restarts == 0
 
 
+def test_host_buffers_over_nvlink(world):
+    """large host buffers (numpy, pinned torch) are chunked through H2D | fused kernel | D2H, also across a kill"""
+    res = _run(["30000", "hostpipe=1", "rabit_device_host_min=1M", "rabit_device_host_chunk=1M", "mock=1,1,8,0",
+                "rabit_timeout=1", "rabit_timeout_sec=120"], world, timeout=600)
+    assert res.ok, {i: o[-2500:] for i, o in res.outputs.items()}
+    assert res.restarts == 1
+    assert any("kernel launches" in m for m in res.messages)
+
+
 def test_arena_grows_on_demand(world):
     """a message larger than the current stage makes every rank re-allocate and re-exchange its arena"""
     res = _run(["50000", "iters=2", "grow=1"], world, timeout=600)
