@@ -216,6 +216,8 @@ class RobustEngine : public BaseEngine {
     std::string key;
   };
   void RunOp(OpArgs *a);
+  /*! \brief called before every chunk op after the first of a chunked host-buffer allreduce (fault injection point) */
+  virtual void BetweenChunks() {}
   /*! \brief large host buffers: chunked H2D | device collective | D2H pipeline (engine_ops.cc); false = not taken */
   bool HostViaDevice(void *buf, size_t type_nbytes, size_t count, ReduceFunction reducer, int dtype, int op,
                      const std::string &key);
@@ -301,6 +303,7 @@ class MockEngine : public RobustEngine {
  private:
   /*! \brief die here if (rank, version, seq, trial) was scripted */
   void Verify(const char *what);
+  void BetweenChunks() override { Verify("AllReduce chunk"); }
   double tsum_allreduce_ = 0.0, tsum_allgather_ = 0.0, time_checkpoint_ = 0.0;
 };
 

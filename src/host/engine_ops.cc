@@ -193,6 +193,7 @@ bool RobustEngine::HostViaDevice(void *buf, size_t type_nbytes, size_t count, Re
     if (i + depth < nchunk) {
       device_->PrefetchH2D(dev + begin(i + depth), host + begin(i + depth), span(i + depth), static_cast<int>(i + depth));
     }
+    if (i != 0) BetweenChunks();
     OpArgs a{};
     a.kind = OpKind::kAllreduce; a.buf = dev + begin(i); a.bytes = span(i);
     a.elem_bytes = type_nbytes; a.count = span(i) / type_nbytes; a.reducer = reducer; a.dtype = dtype; a.op = op;
