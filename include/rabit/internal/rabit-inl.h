@@ -46,14 +46,14 @@ struct Max {
   static const engine::mpi::OpType kType = engine::mpi::kMax;
   template <typename T>
   RABIT_HOST_DEVICE static void Reduce(T &dst, const T &src) {  // NOLINT(*)
-    if (dst < src) dst = src;
+    dst = dst < src ? src : dst;  // unconditional store: the host loop below vectorises (maxps / pmax)
   }
 };
 struct Min {
   static const engine::mpi::OpType kType = engine::mpi::kMin;
   template <typename T>
   RABIT_HOST_DEVICE static void Reduce(T &dst, const T &src) {  // NOLINT(*)
-    if (src < dst) dst = src;
+    dst = src < dst ? src : dst;
   }
 };
 struct Sum {
@@ -73,8 +73,9 @@ struct BitOR {
 /*! \brief host reducer with the engine's ReduceFunction signature */
 template <typename OP, typename T>
 inline void Reducer(const void *src_, void *dst_, int len, const MPI::Datatype &) {
-  const T *src = static_cast<const T *>(src_);
-  T *dst = static_cast<T *>(dst_);
+  // the engine never folds a buffer into itself
+  const T *__restrict__ src = static_cast<const T *>(src_);
+  T *__restrict__ dst = static_cast<T *>(dst_);
   for (int i = 0; i < len; ++i) OP::Reduce(dst[i], src[i]);
 }
 }  // namespace op

@@ -445,9 +445,10 @@ Status HostComm::AllgatherRing(void *buf_, size_t total, size_t slice_begin, siz
   return Status::kOk;
 }
 
-Status HostComm::ReduceScatterRing(void *buf_, size_t eb, size_t count, ReduceFunction *reducer) {
+Status HostComm::ReduceScatterRing(void *buf_, size_t eb, size_t count, ReduceFunction *reducer, const void *src_) {
   if (ring_prev_ == nullptr || ring_next_ == nullptr || count == 0) return Status::kOk;
   char *buf = static_cast<char *>(buf_);
+  const char *src = src_ != nullptr && src_ != buf_ ? static_cast<const char *>(src_) : nullptr;
   const size_t n = static_cast<size_t>(world);
   const size_t step = (count + n - 1) / n;
   const size_t total = count * eb;
@@ -493,13 +494,17 @@ Status HostComm::ReduceScatterRing(void *buf_, size_t eb, size_t count, ReduceFu
       const size_t pos = (recv_start + reduced) % total;
       size_t len = std::min(avail - reduced, cap - off);
       len = std::min(len, total - pos);
+      if (src != nullptr) std::memcpy(buf + pos, src + pos, len);  // our share of this piece, cache-hot for the fold
       reducer(stage + off, buf + pos, static_cast<int>(len / eb), dtype);
       reduced += len;
     }
     sendable = std::min(total_send, head + reduced);
     if (sent < sendable && poll.CheckWrite(ring_prev_->sock.fd)) {
       const size_t pos = (send_start + sent) % total;
-      size_t put; Status s = SendSome(ring_prev_, buf + pos, std::min(sendable - sent, total - pos), &put);
+      // the first `head` bytes of the stream are our own untouched data, the rest are folded partial sums
+      const bool own = src != nullptr && sent < head;
+      const size_t upto = own ? std::min(sendable, head) : sendable;
+      size_t put; Status s = SendSome(ring_prev_, (own ? src : buf) + pos, std::min(upto - sent, total - pos), &put);
       if (!Ok(s)) return s;
       sent += put;
     }
@@ -507,8 +512,17 @@ Status HostComm::ReduceScatterRing(void *buf_, size_t eb, size_t count, ReduceFu
   return Status::kOk;
 }
 
-Status HostComm::AllreduceRing(void *buf, size_t eb, size_t count, ReduceFunction *reducer) {
-  Status s = ReduceScatterRing(buf, eb, count, reducer);
+Status HostComm::AllreduceFrom(const void *src, void *dst, size_t eb, size_t count, ReduceFunction *reducer) {
+  if (count == 0) return Status::kOk;
+  if (world <= 1 || count <= cfg.reduce_ring_mincount || src == dst) {
+    if (src != dst) std::memcpy(dst, src, eb * count);
+    return Allreduce(dst, eb, count, reducer);
+  }
+  return AllreduceRing(dst, eb, count, reducer, src);
+}
+
+Status HostComm::AllreduceRing(void *buf, size_t eb, size_t count, ReduceFunction *reducer, const void *src) {
+  Status s = ReduceScatterRing(buf, eb, count, reducer, src);
   if (!Ok(s)) return s;
   const size_t n = static_cast<size_t>(world);
   const size_t step = (count + n - 1) / n;

@@ -81,8 +81,16 @@ class HostComm {
   // ---- collectives on host memory ----
   Status Allreduce(void *buf, size_t elem_bytes, size_t count, ReduceFunction *reducer);
   Status AllreduceTree(void *buf, size_t elem_bytes, size_t count, ReduceFunction *reducer);
-  Status AllreduceRing(void *buf, size_t elem_bytes, size_t count, ReduceFunction *reducer);
-  Status ReduceScatterRing(void *buf, size_t elem_bytes, size_t count, ReduceFunction *reducer);
+  Status AllreduceRing(void *buf, size_t elem_bytes, size_t count, ReduceFunction *reducer, const void *src = nullptr);
+  /*!
+   * \brief ring reduce-scatter. With src == NULL it works in place on buf; otherwise src holds this rank's
+   *  contribution, stays untouched, and buf only receives: own data leaves straight from src and every
+   *  segment is copied over piecewise right before it is folded (no whole-message copy up front).
+   */
+  Status ReduceScatterRing(void *buf, size_t elem_bytes, size_t count, ReduceFunction *reducer,
+                           const void *src = nullptr);
+  /*! \brief out-of-place allreduce: reads src, leaves the result in dst, src is never written (src may equal dst) */
+  Status AllreduceFrom(const void *src, void *dst, size_t elem_bytes, size_t count, ReduceFunction *reducer);
   Status AllgatherRing(void *buf, size_t total, size_t slice_begin, size_t slice_end,
                        size_t size_prev_slice);
   Status Broadcast(void *buf, size_t size, int root);

@@ -37,7 +37,7 @@ struct Config {
   int nport_trial = 1000;
   // ---- host collectives ----
   size_t tree_reduce_minsize = 1 << 20;      // bytes per pipeline chunk in the tree
-  size_t reduce_ring_mincount = 32 << 10;    // elements; above this the ring is used
+  size_t reduce_ring_mincount = 256 << 10;   // elements; above this the ring is used (reference: 32 Ki; see doc/parameters.md)
   size_t reduce_buffer = 256UL << 20;        // cap of a per-link staging ring
   bool tcp_no_delay = true;                  // reference default is off (Nagle stalls)
   int hadoop_mode = 0;

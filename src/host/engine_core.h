@@ -132,12 +132,42 @@ inline size_t DTypeBytes(int dtype) {
  *  host memory or in GPU memory (written there by the collective kernel's epilogue); a host
  *  view of a device entry is materialised only if a peer actually asks for it.
  */
+/*!
+ * \brief host bytes of a cache entry: uninitialised and recycled. A fresh std::string per collective costs a
+ *  zero fill plus one page fault per 4 KiB of a large message every time; blocks of 64 KiB and more therefore
+ *  go back to a small per-thread pool and are handed out again, still mapped.
+ */
+class HostBytes {
+ public:
+  HostBytes() {}
+  HostBytes(HostBytes &&o) noexcept : p_(o.p_), size_(o.size_), cap_(o.cap_) { o.p_ = nullptr; o.size_ = o.cap_ = 0; }
+  HostBytes &operator=(HostBytes &&o) noexcept {
+    if (this != &o) { clear(); p_ = o.p_; size_ = o.size_; cap_ = o.cap_; o.p_ = nullptr; o.size_ = o.cap_ = 0; }
+    return *this;
+  }
+  HostBytes(const HostBytes &) = delete;
+  HostBytes &operator=(const HostBytes &) = delete;
+  ~HostBytes() { clear(); }
+  /*! \brief make room for n bytes; the content is NOT preserved and NOT initialised */
+  void resize(size_t n);
+  /*! \brief give the block back */
+  void clear();
+  char *data() { return p_; }
+  const char *data() const { return p_; }
+  size_t size() const { return size_; }
+  char &operator[](size_t i) { return p_[i]; }
+
+ private:
+  char *p_ = nullptr;
+  size_t size_ = 0, cap_ = 0;
+};
+
 class ResultStore {
  public:
   struct Entry {
     int seq = -1;
     size_t bytes = 0;
-    std::string host;
+    HostBytes host;
     void *dev = nullptr;
   };
   ~ResultStore() { Clear(); }
@@ -221,7 +251,7 @@ class RobustEngine : public BaseEngine {
   /*! \brief large host buffers: chunked H2D | device collective | D2H pipeline (engine_ops.cc); false = not taken */
   bool HostViaDevice(void *buf, size_t type_nbytes, size_t count, ReduceFunction reducer, int dtype, int op,
                      const std::string &key);
-  Status TryOp(const OpArgs &a, char *slot);
+  Status TryOp(const OpArgs &a, char *slot, const char *input);
 
   /*!
    * \brief the consensus loop. Returns true when the request was satisfied by recovery

@@ -18,11 +18,19 @@ void RobustEngine::DropStaleResult() {
   if (round == -1 || last % round != comm_.rank % round) results_.DropLast();
 }
 
-Status RobustEngine::TryOp(const OpArgs &a, char *slot) {
+/*!
+ * One attempt of the transfer, out of place: `input` (the caller's bytes) is only read, the result is built
+ * in the cache slot. A failure half-way therefore leaves the caller's buffer intact for the retry, and no
+ * whole-message copy is needed up front: only the bytes this rank actually contributes are taken over.
+ */
+Status RobustEngine::TryOp(const OpArgs &a, char *slot, const char *input) {
   switch (a.kind) {
-    case OpKind::kAllreduce: return comm_.Allreduce(slot, a.elem_bytes, a.count, a.reducer);
-    case OpKind::kBroadcast: return comm_.Broadcast(slot, a.bytes, a.root);
+    case OpKind::kAllreduce: return comm_.AllreduceFrom(input, slot, a.elem_bytes, a.count, a.reducer);
+    case OpKind::kBroadcast:
+      if (comm_.rank == a.root) std::memcpy(slot, input, a.bytes);
+      return comm_.Broadcast(slot, a.bytes, a.root);
     case OpKind::kAllgather:
+      std::memcpy(slot + a.slice_begin, input + a.slice_begin, a.slice_end - a.slice_begin);
       return comm_.AllgatherRing(slot, a.bytes, a.slice_begin, a.slice_end, a.size_prev_slice);
   }
   return Status::kSockError;
@@ -134,12 +142,14 @@ void RobustEngine::RunOp(OpArgs *a) {
     prepare_once();
     slot = results_.AllocTemp(a->bytes);
     if (on_device) to_host(view, a->buf, a->bytes);
-    std::memcpy(slot, view, a->bytes);
-    // the transfer works on the cache slot so that a failure half-way leaves the caller's buffer
-    // intact for the retry
-    if (Healthy(TryOp(*a, slot))) {
-      std::memcpy(view, slot, a->bytes);
-      if (on_device) to_device(a->buf, view, a->bytes);
+    // the transfer builds its result in the cache slot so that a failure half-way leaves the caller's
+    // buffer intact for the retry
+    if (Healthy(TryOp(*a, slot, view))) {
+      // (the root of a broadcast already holds the result)
+      if (!(a->kind == OpKind::kBroadcast && comm_.rank == a->root)) {
+        std::memcpy(view, slot, a->bytes);
+        if (on_device) to_device(a->buf, view, a->bytes);
+      }
       break;
     }
   }
