@@ -38,7 +38,7 @@ std::vector<char *> Argv(std::vector<std::string> &v) {  // NOLINT(*)
 // ---- parameters (parity: allreduce_base_test.cc) ----
 TEST(config_defaults_and_argv) {
   Config c;
-  EXPECT(c.tracker_uri == "NULL" && c.tracker_port == 9000 && c.reduce_ring_mincount == (32u << 10));
+  EXPECT(c.tracker_uri == "NULL" && c.tracker_port == 9000 && c.reduce_ring_mincount == (256u << 10));
   std::vector<std::string> a = {"prog", "rabit_task_id=7", "rabit_bootstrap_cache=1", "rabit_debug=true",
                                 "rabit_reduce_ring_mincount=10", "rabit_reduce_buffer=16K", "mock=1,2,3,4",
                                 "mock=0,0,1,0", "rabit_timeout=1", "rabit_timeout_sec=7", "notaparam", "=x"};
