@@ -192,7 +192,15 @@ bool HostComm::Connect(const char *cmd) {
     if (ring_prev_rank >= 0) expected.push_back(ring_prev_rank);
     if (ring_next_rank >= 0) expected.push_back(ring_next_rank);
     std::vector<int> accepted;
+    // A peer that died between the tracker's plan and its dial would leave us in accept() for good (the
+    // reference blocks there, allreduce_base.cc:420-436); give up after a while so that the caller goes back
+    // to the tracker, where the replacement process will turn up.
+    const int accept_wait_ms = 1000 * (cfg.timeout_enabled ? std::max(cfg.timeout_sec, 1) : 300);
     while (static_cast<int>(accepted.size()) < naccept) {
+      utils::PollHelper incoming;
+      incoming.WatchRead(listener.fd);
+      utils::Check(incoming.Poll(accept_wait_ms) != 0, "gave up waiting for %d more neighbour(s) to connect",
+                   naccept - static_cast<int>(accepted.size()));
       Link nl;
       nl.sock = listener.Accept();
       int intended = -1;
