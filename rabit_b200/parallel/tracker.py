@@ -138,6 +138,7 @@ class Tracker(object):
         self.host = host
         self.port = self.sock.getsockname()[1]
         self.verbose = verbose
+        self.io_timeout = 120.0     # seconds a worker may stay silent in the middle of an exchange
         self.messages = []          # lines received through "print"
         self.thread = None
         self.error = None
@@ -208,6 +209,7 @@ class Tracker(object):
             # the protocol is a chain of tiny writes followed by a read: without TCP_NODELAY every such
             # exchange stalls ~40 ms in Nagle + delayed ACK, which dominated recover-after-kill time
             fd.setsockopt(socket.IPPROTO_TCP, socket.TCP_NODELAY, 1)
+            fd.settimeout(self.io_timeout)   # a frozen worker must not freeze the (single-threaded) tracker
             c = _Conn(fd, addr)
             try:
                 c.handshake()
@@ -235,13 +237,24 @@ class Tracker(object):
                     if len(pending) == len(todo):
                         # hand out ranks in one go; sorting by host keeps co-located workers adjacent
                         pending.sort(key=lambda x: x.host)
-                        for p in pending:
+                        batch, pending = pending, []
+                        for p in batch:
                             r = todo.pop(0)
                             if p.task_id != "NULL":
                                 job_rank[p.task_id] = r
-                            self._assign(p, r, tree, parent, ring, wait_conn)
-                            p.sock.close()
-                        pending = []
+                            try:
+                                self._assign(p, r, tree, parent, ring, wait_conn)
+                            except (ConnectionError, OSError, struct.error) as e:
+                                # died while parked: its replacement finds the rank through its task id,
+                                # or (no task id) takes it from the free list again
+                                log.warning("tracker: worker for rank %d vanished during assignment: %s", r, e)
+                                if p.task_id == "NULL":
+                                    todo.append(r)
+                            finally:
+                                try:
+                                    p.sock.close()
+                                except OSError:
+                                    pass
                     continue
                 # a restarted worker ("start") or a survivor re-joining ("recover")
                 log.debug("%s rank %d (task %s); parked: %s", c.cmd, rank, c.task_id,

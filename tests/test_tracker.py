@@ -34,3 +34,53 @@ def test_topology_invariants(n):
     for r in range(n):
         if parent[r] != -1:
             assert parent[r] in tree[r]
+
+
+def _raw(tracker):
+    import socket
+    s = socket.create_connection((tracker.host, tracker.port))
+    s.setsockopt(socket.IPPROTO_TCP, socket.TCP_NODELAY, 1)
+    return s
+
+
+def test_tracker_survives_broken_clients(built):
+    """Half-open handshakes, a wrong magic and a worker that dies while parked for the batch rank assignment
+    must not take the (single-threaded) tracker down; the job that follows still rendezvouses and its
+    replacement worker gets the rank of the one that vanished."""
+    import os
+    import struct
+    import subprocess
+    from conftest import bin_path
+    from rabit_b200.parallel.tracker import Tracker, MAGIC
+
+    t = Tracker(2).start()
+    try:
+        s = _raw(t); s.close()                                         # connects, says nothing
+        s = _raw(t); s.sendall(struct.pack("@i", 0x1234)); s.close()   # wrong magic
+        s = _raw(t); s.sendall(struct.pack("@i", MAGIC)); s.recv(4); s.sendall(struct.pack("@i", -1)); s.close()
+        # a first-time worker that parks for the batch assignment and then dies
+        ghost = _raw(t)
+        task = b"0"
+        ghost.sendall(struct.pack("@i", MAGIC))
+        ghost.recv(4)
+        ghost.sendall(struct.pack("@iii", -1, 2, len(task)) + task + struct.pack("@i", 5) + b"start")
+        procs = []
+        env = dict(os.environ)
+        env.update(t.worker_env())
+        env["DMLC_TASK_ID"] = "1"
+        env["DMLC_NUM_ATTEMPT"] = "0"
+        procs.append(subprocess.Popen([bin_path("basic")], env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT))
+        import time
+        time.sleep(0.5)
+        ghost.close()      # the tracker notices when it tries to hand it rank 0
+        env0 = dict(env)
+        env0["DMLC_TASK_ID"] = "0"
+        env0["rabit_timeout"] = "1"
+        env["rabit_timeout"] = "1"
+        procs.append(subprocess.Popen([bin_path("basic")], env=env0, stdout=subprocess.PIPE, stderr=subprocess.STDOUT))
+        outs = [p.communicate(timeout=120)[0].decode(errors="replace") for p in procs]
+        assert [p.returncode for p in procs] == [0, 0], outs
+        assert t.join(30), "tracker did not see both shutdowns"
+        assert t.error is None
+    finally:
+        t.close()
