@@ -6,6 +6,9 @@ cd "$(dirname "$0")/.."
 python build.py
 ./build/bin/unit_tests
 python -m pytest tests -x -q -m "not gpu"
+# fault scenarios of the host engine under ASan+UBSan and TSan (static sanitizer builds in build/san_*)
+python scripts/sanitize.py address
+python scripts/sanitize.py thread
 if python -c "import torch,sys; sys.exit(0 if torch.cuda.is_available() else 1)"; then
   python -m pytest tests -x -q -m gpu
   python __graft_entry__.py smoke
