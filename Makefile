@@ -1,5 +1,5 @@
 # rabit-b200: thin make front end over build.py (in-tree build of lib/*.so and build/bin/*)
-.PHONY: all host test gputest clean lint
+.PHONY: all host test gputest clean lint sanitize
 all:
 	python build.py
 host:
@@ -10,3 +10,7 @@ gputest: all
 	python -m pytest tests -x -q -m gpu
 clean:
 	python build.py --clean
+lint:
+	python scripts/lint.py
+sanitize:
+	python scripts/sanitize.py address && python scripts/sanitize.py thread

@@ -3,6 +3,7 @@
 # CPU test tier, and — when a GPU is visible — the GPU tier.
 set -euo pipefail
 cd "$(dirname "$0")/.."
+python scripts/lint.py
 python build.py
 ./build/bin/unit_tests
 python -m pytest tests -x -q -m "not gpu"
