@@ -213,6 +213,26 @@ TEST(result_store_semantics) {
   EXPECT(rs.Count() == 0 && rs.LastSeq() == -1);
 }
 
+TEST(host_bytes_blocks_are_recycled) {
+  // medium (slab) and large blocks come back from the pool still mapped; small ones are plain malloc
+  for (size_t n : {size_t(100) << 10, size_t(5) << 20}) {
+    HostBytes a; a.resize(n);
+    EXPECT(a.size() == n && a.data() != nullptr);
+    std::memset(a.data(), 7, n);
+    char *first = a.data();
+    a.clear();
+    EXPECT(a.size() == 0 && a.data() == nullptr);
+    HostBytes b; b.resize(n - 100);   // close enough in size: same block again
+    EXPECT(b.data() == first && b.size() == n - 100);
+    HostBytes c(std::move(b));
+    EXPECT(c.data() == first && b.data() == nullptr);
+    HostBytes d; d.resize(n);         // the first block is taken: a different one
+    EXPECT(d.data() != first);
+  }
+  HostBytes s; s.resize(10); s.resize(4); EXPECT(s.size() == 4);
+  s.resize(0); EXPECT(s.size() == 0);
+}
+
 // ---- consensus decision table ----
 using namespace rabit::engine::proto;  // NOLINT(*)
 static Summary Fold(const std::vector<Request> &rs) {
