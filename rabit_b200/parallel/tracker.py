@@ -229,6 +229,13 @@ class Tracker(object):
                     raise ConnectionError("unknown tracker command %r" % c.cmd)
                 if self.start_time is None:
                     self.start_time = time.time()
+                if c.cmd == "recover" and shutdown:
+                    # Some ranks have left for good, so a full re-rendezvous can never complete. This only happens
+                    # when the final barrier round succeeded on part of the ranks and failed on the caller: tell it
+                    # the job is over instead of parking it for ever (rank -2; not part of the reference protocol,
+                    # whose workers would block here).
+                    c.sock.sendall(struct.pack("@3i", -2, -1, n))
+                    continue
                 rank = c.rank
                 if rank < 0 and c.task_id != "NULL":
                     rank = job_rank.get(c.task_id, -1)

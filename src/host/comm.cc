@@ -125,6 +125,11 @@ bool HostComm::Connect(const char *cmd) {
     int new_rank = -1, nnbr = 0;
     utils::Check(t.RecvInt(&new_rank) && t.RecvInt(&parent_rank) && t.RecvInt(&world),
                  "tracker: cannot read assignment");
+    if (new_rank == -2) {
+      // our tracker's way of saying: peers have shut down for good, there is nothing to re-join
+      job_over = true;
+      utils::Error("the job is over: other ranks have already shut down");
+    }
     utils::Check(new_rank >= 0, "tracker refused to assign a rank");
     utils::Assert(!rank_assigned_ || new_rank == rank, "tracker changed our rank from %d to %d", rank, new_rank);
     rank = new_rank; rank_assigned_ = true; world_known_ = true;

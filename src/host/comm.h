@@ -59,6 +59,8 @@ class HostComm {
   std::string host;
   /*! \brief bumped on every successful (re)connect; device backend keys its mappings on it */
   int link_generation = 0;
+  /*! \brief set when the tracker answers a "recover" with "the job is over" (peers have shut down) */
+  bool job_over = false;
 
   bool distributed() const { return cfg.tracker_uri != "NULL"; }
 

@@ -298,7 +298,7 @@ int RobustEngine::LoadCheckPoint(Serializable *global_model, Serializable *local
                   version_number_);
   }
   // survivors stay parked until we acknowledge, so that they cannot run ahead and drop state
-  utils::Assert(Consensus(nullptr, 0, proto::kCheckAck, proto::kSeqSpecial), "load ack");
+  utils::Assert(Consensus(nullptr, 0, proto::kLoadAck, proto::kSeqSpecial), "load ack");
   if (comm_.cfg.debug) {
     utils::HandleLogInfo("[%d] loadcheckpoint size %lu finished version %d, seq %d, take %f seconds\n",
                          comm_.rank, static_cast<unsigned long>(global_blob_.size()),  // NOLINT(*)

@@ -59,6 +59,13 @@ bool RobustEngine::Shutdown(void) {
     results_.SetDevice(nullptr);
     return BaseEngine::Shutdown();
   } catch (const std::exception &e) {
+    if (comm_.job_over) {
+      // the final barrier round reached the others but not us; they are gone and so is any need for our cache
+      StopWatchdog();
+      results_.Clear();
+      results_.SetDevice(nullptr);
+      return BaseEngine::Shutdown();
+    }
     fprintf(stderr, "[rabit] shutdown: %s\n", e.what());
     return false;
   }
@@ -114,7 +121,10 @@ bool RobustEngine::Healthy(Status s) {
   if (device_) device_->Detach();
   comm_.CloseLinks();
   std::this_thread::sleep_for(std::chrono::milliseconds(2 * comm_.rank));
-  while (!comm_.Connect("recover")) std::this_thread::sleep_for(std::chrono::milliseconds(100));
+  while (!comm_.Connect("recover")) {
+    utils::Check(!comm_.job_over, "[%d] cannot recover: the other ranks have already shut down", comm_.rank);
+    std::this_thread::sleep_for(std::chrono::milliseconds(100));
+  }
   if (device_ && !device_->Attach(&comm_)) {
     utils::Error("[%d] device arena could not be re-established after recovery", comm_.rank);
   }

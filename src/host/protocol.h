@@ -8,7 +8,7 @@
  *
  * This plays the role of the reference's ActionSummary + RecoverExec pair
  * (allreduce_robust.h:224-322, allreduce_robust.cc:1158-1311). It is re-derived, not
- * transcribed: priorities are explicit (ack > bootstrap-cache > load > sequence order),
+ * transcribed: priorities are explicit (load-ack > commit-ack > bootstrap-cache > load > sequence order),
  * the bootstrap cache is compared by entry count, and "who holds the bytes" is NOT part
  * of the summary — holders are discovered afterwards with a per-rank table gather and the
  * bytes move along the rank ring (see RobustEngine::Serve*).
@@ -34,6 +34,7 @@ const uint32_t kLoadCheck = 1;    // wants the latest checkpoint (LoadCheckPoint
 const uint32_t kCheckPoint = 2;   // waiting at commit barrier 1
 const uint32_t kCheckAck = 4;     // waiting at commit barrier 2
 const uint32_t kLoadCache = 8;    // bootstrap phase: wants/offers the pre-checkpoint op cache
+const uint32_t kLoadAck = 16;     // a restarted rank has finished loading; parks everybody else for one round
 const uint32_t kFlagBits = 5;
 const uint32_t kFlagMask = (1u << kFlagBits) - 1;
 
@@ -121,13 +122,22 @@ struct Verdict {
 inline Verdict Decide(const Summary &s, const Request &me) {
   const bool i_load = me.flags & kLoadCheck, i_ckpt = me.flags & kCheckPoint;
   const bool i_ack = me.flags & kCheckAck, i_cache = me.flags & kLoadCache;
-  // 1. Somebody already passed commit barrier 1. Ranks still knocking at barrier 1 only got a
-  //    failed consensus round: let them through first, then serve loaders (they will see the
-  //    NEW version), then release the ackers.
-  if (s.any(kCheckAck)) {
-    if (s.any(kCheckPoint)) return Verdict{i_ckpt ? kDone : kRetry, false};
+  // 1. Acknowledgements. kCheckAck: somebody already passed commit barrier 1. kLoadAck: a restarted rank holds the
+  //    checkpoint now (survivors are parked until then, so that they cannot run ahead and drop state it is still
+  //    copying). The reference uses ONE flag for both (allreduce_robust.cc:438-441 and :549-552); that lets a rank
+  //    waiting at commit barrier 1 slip through on a loader's acknowledgement while a third rank is still inside the
+  //    version's last collective, and the rank that committed then drops results the others still need.
+  //    Ranks still knocking at barrier 1 of the SAME commit only got a failed consensus round: they go first,
+  //    then loaders are served (they will see the NEW version), then everybody who acknowledged leaves together.
+  const bool i_loadack = me.flags & kLoadAck;
+  if (s.any(kCheckAck | kLoadAck)) {
+    if (s.any(kCheckPoint)) {
+      if (s.any(kCheckAck)) return Verdict{i_ckpt ? kDone : kRetry, false};
+      // only a loader acknowledged: the knockers belong to a commit that has not begun
+      return Verdict{i_loadack ? kDone : kRetry, false};
+    }
     if (s.any(kLoadCheck)) return Verdict{kServeLoad, i_load};
-    return Verdict{i_ack ? kDone : kRetry, false};
+    return Verdict{(i_ack || i_loadack) ? kDone : kRetry, false};
   }
   // 2. Bootstrap phase (collectives issued before LoadCheckPoint).
   if (s.any(kLoadCache)) {

@@ -275,6 +275,21 @@ TEST(decide_load_checkpoint) {
   // ack phase: load is served with the new version before ackers leave
   s = Fold({ld, ack});
   EXPECT(Decide(s, ack).action == kServeLoad && !Decide(s, ack).requester && Decide(s, ld).requester);
+  // the loader's own acknowledgement releases the loader only: a rank at commit barrier 1 must NOT slip through
+  // on it while a third rank is still inside the version's last collective
+  Request lack{kSeqSpecial, kLoadAck, 0};
+  s = Fold({lack, ck, op3});
+  EXPECT(Decide(s, lack).action == kDone && Decide(s, ck).action == kRetry && Decide(s, op3).action == kRetry);
+  s = Fold({lack, ck, ck});
+  EXPECT(Decide(s, lack).action == kDone && Decide(s, ck).action == kRetry);
+  // loaded the new version from ranks parked at barrier 2: everybody who acknowledged leaves in the same round
+  // (a loader released alone could reach the NEXT commit while the others still wait at barrier 2 of this one)
+  s = Fold({lack, ack, ack});
+  EXPECT(Decide(s, lack).action == kDone && Decide(s, ack).action == kDone);
+  s = Fold({lack, ack, ck});    // a knocker of the same commit goes first
+  EXPECT(Decide(s, ck).action == kDone && Decide(s, lack).action == kRetry && Decide(s, ack).action == kRetry);
+  s = Fold({lack, ld, op3});    // a second rank is still loading: it is served before anybody leaves
+  EXPECT(Decide(s, ld).action == kServeLoad && Decide(s, ld).requester && !Decide(s, lack).requester);
 }
 TEST(decide_bootstrap_cache) {
   Request b0{0, kLoadCache, 0}, b1{0, kLoadCache, 1}, op2{2, 0, 1}, ld{kSeqSpecial, kLoadCheck, 1};

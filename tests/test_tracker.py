@@ -84,3 +84,33 @@ def test_tracker_survives_broken_clients(built):
         assert t.error is None
     finally:
         t.close()
+
+
+def test_tracker_tells_late_recoverer_that_the_job_is_over():
+    """once a rank has shut down a full re-rendezvous can never complete: "recover" is answered with rank -2"""
+    import struct
+    from rabit_b200.parallel.tracker import Tracker, MAGIC
+
+    def hello(t, rank, cmd):
+        s = _raw(t)
+        s.sendall(struct.pack("@i", MAGIC))
+        assert struct.unpack("@i", s.recv(4))[0] == MAGIC
+        task = str(rank).encode()
+        s.sendall(struct.pack("@iii", rank, 2, len(task)) + task + struct.pack("@i", len(cmd)) + cmd.encode())
+        return s
+
+    t = Tracker(2).start()
+    try:
+        hello(t, 0, "shutdown").close()
+        s = hello(t, 1, "recover")
+        got = b""
+        while len(got) < 12:
+            chunk = s.recv(12 - len(got))
+            assert chunk, "tracker closed without answering"
+            got += chunk
+        assert struct.unpack("@3i", got) == (-2, -1, 2)
+        s.close()
+        hello(t, 1, "shutdown").close()
+        assert t.join(20) and t.error is None
+    finally:
+        t.close()
