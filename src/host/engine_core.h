@@ -301,6 +301,9 @@ class RobustEngine : public BaseEngine {
   bool in_sync_ = false;
   std::string global_blob_;                  // [int32 version][Save bytes]
   const Serializable *lazy_model_ = nullptr;
+  /*! \brief inside Commit/Shutdown, before barrier 1 has passed: the caller has already moved its model on to the
+   *  NEXT version, so a lazy checkpoint pointer must not be serialised for a loader of the current one */
+  bool at_barrier1_ = false;
   // local models: slot j holds the blob of rank (me - j); two generations
   std::vector<std::string> local_[2];
   std::vector<char> local_has_[2];

@@ -332,7 +332,9 @@ void RobustEngine::Commit(const Serializable *global_model, const Serializable *
     Consensus(nullptr, 0, 0, proto::kSeqLocalAck);
   }
   // barrier 1: everybody has finished the version's collectives
+  at_barrier1_ = true;
   utils::Assert(Consensus(nullptr, 0, proto::kCheckPoint, proto::kSeqSpecial), "commit barrier 1");
+  at_barrier1_ = false;
   // ---- the commit itself: purely local, identical on all ranks ----
   ++version_number_;
   if (num_local_replica_ != 0) local_gen_ = next_gen;

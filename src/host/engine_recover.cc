@@ -91,7 +91,11 @@ Status RobustEngine::ServeLoad(bool requester) {
     Status st = CompleteLocal(local_gen_);
     if (!Ok(st)) return st;
   }
-  const bool holder = !requester && checkpoint_loaded_;
+  // A rank waiting at commit barrier 1 has finished the version: under the LazyCheckPoint contract its model object
+  // already holds the NEXT version, so it cannot serialise the current one any more. Ranks that are still inside
+  // the version can (there is at least one, otherwise the commit would have gone first, see proto::Decide).
+  const bool stale_lazy = lazy_model_ != nullptr && at_barrier1_;
+  const bool holder = !requester && checkpoint_loaded_ && !stale_lazy;
   if (holder) MaterializeLazy();  // a lazy checkpoint is serialised the first time anyone asks
   uint64_t row[3] = {holder ? 1u : 0u, requester ? 1u : 0u, holder ? global_blob_.size() : 0};
   std::vector<uint64_t> tab;

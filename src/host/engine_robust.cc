@@ -50,6 +50,9 @@ bool RobustEngine::Shutdown(void) {
   try {
     if (comm_.world > 1) {
       // Leave through a pseudo commit so nobody exits while a peer still needs its cache.
+      // A lazy checkpoint is serialised now: the model it points to is still intact (no collective followed the
+      // last LazyCheckPoint) but may be destroyed by the caller right after Finalize.
+      MaterializeLazy();
       utils::Assert(Consensus(nullptr, 0, proto::kCheckPoint, proto::kSeqSpecial), "shutdown barrier 1");
       results_.Clear(); seq_ = 0; boot_cache_.clear();
       utils::Assert(Consensus(nullptr, 0, proto::kCheckAck, proto::kSeqSpecial), "shutdown barrier 2");
