@@ -229,12 +229,18 @@ class Tracker(object):
                     raise ConnectionError("unknown tracker command %r" % c.cmd)
                 if self.start_time is None:
                     self.start_time = time.time()
-                if c.cmd == "recover" and shutdown:
+                if shutdown:
                     # Some ranks have left for good, so a full re-rendezvous can never complete. This only happens
-                    # when the final barrier round succeeded on part of the ranks and failed on the caller: tell it
-                    # the job is over instead of parking it for ever (rank -2; not part of the reference protocol,
-                    # whose workers would block here).
+                    # at the very end of a job: the final barrier round reached part of the ranks and failed on the
+                    # caller ("recover"), or a worker was killed after it had taken part in that round and its
+                    # replacement turns up ("start"). Tell it the job is over instead of parking it for ever
+                    # (rank -2; not part of the reference protocol, whose workers would block here).
                     c.sock.sendall(struct.pack("@3i", -2, -1, n))
+                    if c.cmd == "start":
+                        # the replacement exits on this answer: count the rank it stands for as gone
+                        gone = c.rank if c.rank >= 0 else job_rank.get(c.task_id, -1)
+                        if gone >= 0:
+                            shutdown.add(gone)
                     continue
                 rank = c.rank
                 if rank < 0 and c.task_id != "NULL":

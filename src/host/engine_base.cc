@@ -45,7 +45,15 @@ bool BaseEngine::Init(int argc, char *argv[]) {
     exit(0);
   }
   comm_.host = utils::SockAddr::GetHostName();
-  if (!comm_.Connect("start")) return false;
+  if (!comm_.Connect("start")) {
+    if (comm_.job_over) {
+      // A replacement process that arrives after its peers have left: they could only leave because every rank,
+      // the one we replace included, had reached the final barrier. Nothing is left to compute or to re-join.
+      fprintf(stderr, "[rabit] the job finished while this worker was being restarted; nothing to re-join, exit 0\n");
+      exit(0);
+    }
+    return false;
+  }
   if (comm_.world > 1 || comm_.cfg.device_force) {
     device_.reset(DeviceBackend::Create(comm_.cfg));
     if (device_ && !device_->Attach(&comm_)) {

@@ -114,3 +114,42 @@ def test_tracker_tells_late_recoverer_that_the_job_is_over():
         assert t.join(20) and t.error is None
     finally:
         t.close()
+
+
+def test_replacement_worker_after_the_job_ended_exits_cleanly(built):
+    """a worker killed after the final barrier is restarted by the launcher; its peers are gone: the tracker says so,
+    the replacement exits 0 and the tracker counts the rank as finished"""
+    import os
+    import struct
+    import subprocess
+    from conftest import bin_path
+    from rabit_b200.parallel.tracker import Tracker, MAGIC
+
+    t = Tracker(2).start()
+    try:
+        env = dict(os.environ)
+        env.update(t.worker_env())
+        procs = []
+        for i in range(2):
+            e = dict(env, DMLC_TASK_ID=str(i), DMLC_NUM_ATTEMPT="0")
+            procs.append(subprocess.Popen([bin_path("basic")], env=e, stdout=subprocess.PIPE, stderr=subprocess.STDOUT))
+        for p in procs:
+            p.communicate(timeout=60)
+        assert [p.returncode for p in procs] == [0, 0]
+        assert t.join(20)
+    finally:
+        t.close()
+    # same, but rank 1 "dies" right after the last barrier: here, its shutdown notice never reaches the tracker
+    t = Tracker(2).start()
+    try:
+        s = _raw(t)   # rank 0 says goodbye
+        s.sendall(struct.pack("@i", MAGIC)); s.recv(4)
+        s.sendall(struct.pack("@iii", 0, 2, 1) + b"0" + struct.pack("@i", 8) + b"shutdown")
+        s.close()
+        e = dict(os.environ, DMLC_TASK_ID="1", DMLC_NUM_ATTEMPT="1")
+        e.update(t.worker_env())
+        p = subprocess.Popen([bin_path("basic")], env=e, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)
+        out = p.communicate(timeout=60)[0].decode(errors="replace")
+        assert p.returncode == 0 and "nothing to re-join" in out, out
+    finally:
+        t.close()
