@@ -141,6 +141,7 @@ class Tracker(object):
         self.io_timeout = 120.0     # seconds a worker may stay silent in the middle of an exchange
         self.messages = []          # lines received through "print"
         self.thread = None
+        self.finished = threading.Event()   # every rank has said "shutdown"
         self.error = None
         self.start_time = None
         self.end_time = None
@@ -204,8 +205,17 @@ class Tracker(object):
         wait_conn = {}         # rank -> conn still expecting accept()s from later arrivals
         pending = []           # first-time workers waiting for the batch rank assignment
         todo = list(range(n))  # ranks not handed out yet
-        while len(shutdown) < n:
-            fd, addr = self.sock.accept()
+        while True:
+            if len(shutdown) >= n and not self.finished.is_set():
+                self.end_time = time.time()
+                self.finished.set()
+            # After the last shutdown notice the tracker lingers until close(): a worker that was killed between
+            # its notice and its exit is restarted by the launcher, and the replacement must get an answer
+            # ("the job is over") rather than a listener nobody serves.
+            try:
+                fd, addr = self.sock.accept()
+            except OSError:
+                break           # close() was called
             # the protocol is a chain of tiny writes followed by a read: without TCP_NODELAY every such
             # exchange stalls ~40 ms in Nagle + delayed ACK, which dominated recover-after-kill time
             fd.setsockopt(socket.IPPROTO_TCP, socket.TCP_NODELAY, 1)
@@ -282,7 +292,8 @@ class Tracker(object):
                         c.sock.close()
                     except OSError:
                         pass
-        self.end_time = time.time()
+        if self.end_time is None:
+            self.end_time = time.time()
 
     def start(self):
         def run():
@@ -296,10 +307,20 @@ class Tracker(object):
         return self
 
     def join(self, timeout=None):
-        self.thread.join(timeout)
-        return not self.thread.is_alive()
+        """Wait until every rank has shut down (or the serving thread died); True if the job is complete."""
+        deadline = None if timeout is None else time.time() + timeout
+        while not self.finished.is_set() and self.thread.is_alive():
+            left = None if deadline is None else deadline - time.time()
+            if left is not None and left <= 0:
+                break
+            self.finished.wait(0.2 if left is None else min(0.2, left))
+        return self.finished.is_set()
 
     def close(self):
+        try:
+            self.sock.shutdown(socket.SHUT_RDWR)   # wakes the accept() of the lingering serve loop
+        except OSError:
+            pass
         try:
             self.sock.close()
         except OSError:
