@@ -91,6 +91,9 @@ if __name__ == "__main__":
         delivered += len(info["kills"])
         if not good:
             fails.append(info)
+            os.makedirs(os.path.join(ROOT, "build"), exist_ok=True)
+            with open(os.path.join(ROOT, "build", "chaos_fail_%d.json" % s), "w") as fo:
+                json.dump(info, fo, indent=1)
             print("FAIL", json.dumps({k: info[k] for k in ("seed", "prog", "world", "args", "kills", "done")}), flush=True)
     print("%d runs, %d kills delivered, %d failures, %.0f s" % (count, delivered, len(fails), time.time() - t0))
     sys.exit(1 if fails else 0)
