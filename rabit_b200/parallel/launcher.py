@@ -1,4 +1,4 @@
-"""Local launcher: tracker + N worker processes on this machine, with restarts.
+"""Launcher: tracker + N worker processes, with restarts; on this machine or over ssh.
 
 Stands in for ``dmlc-submit --cluster local --num-workers N --local-num-attempt K``
 that the reference's tests use (reference test/test.mk:16).  Each worker gets
@@ -10,9 +10,17 @@ non-zero is started again until ``max_attempts`` is reached.
 
     python -m rabit_b200.parallel.launcher -n 4 ./guide/basic.rabit
     python -m rabit_b200.parallel.launcher -n 8 --gpus python my_script.py
+    python -m rabit_b200.parallel.launcher -n 16 --cluster ssh --host-file hosts.txt --tracker-host 10.0.0.1 --gpus ./train
+
+``--cluster ssh`` (the role of ``dmlc-submit --cluster ssh``): ``hosts.txt`` has one ``host[:slots]`` per line,
+tasks are dealt to the hosts slot by slot, each worker is started as ``ssh host 'cd <cwd> && env K=V ... cmd'`` and
+restarted the same way. The tracker runs here and must be reachable from the hosts at ``--tracker-host``.
+With ``--gpus`` a worker uses the GPU with its index ON ITS HOST. Ranks of one host share an NVLink arena; as soon as
+a job spans hosts, device buffers are staged through the TCP collectives.
 """
 import argparse
 import os
+import shlex
 import subprocess
 import sys
 import threading
@@ -40,12 +48,45 @@ class JobResult(object):
         return sum(self.attempts.values())
 
 
-def launch(cmd, nworker, max_attempts=20, env=None, capture=False, timeout=None,
-           per_rank_gpu=False, verbose=False, host="127.0.0.1"):
-    """Run ``cmd`` (argv list) as ``nworker`` local processes under a fresh tracker.
+def read_host_file(path):
+    """``host[:slots]`` per line, ``#`` comments; returns [(host, slots)]."""
+    hosts = []
+    with open(path) as fi:
+        for line in fi:
+            line = line.split("#", 1)[0].strip()
+            if not line:
+                continue
+            name, _, slots = line.partition(":")
+            hosts.append((name.strip(), int(slots) if slots.strip() else 1))
+    if not hosts:
+        raise ValueError("host file %s names no host" % path)
+    return hosts
 
-    per_rank_gpu: export CUDA_VISIBLE_DEVICES/RABIT_LOCAL_RANK so task i uses GPU i.
+
+def place_tasks(hosts, nworker):
+    """Deal tasks to hosts slot by slot; returns [(host, index of the task on that host)] per task."""
+    slots = [(h, k) for h, n in hosts for k in range(n)]
+    if len(slots) < nworker:
+        raise ValueError("%d workers do not fit into %d slots" % (nworker, len(slots)))
+    return slots[:nworker]
+
+
+def ssh_command(ssh, host, cwd, env, cmd):
+    """argv that runs ``cmd`` with ``env`` in ``cwd`` on ``host``."""
+    remote = "cd %s && env %s %s" % (shlex.quote(cwd), " ".join("%s=%s" % (k, shlex.quote(v)) for k, v in sorted(env.items())),
+                                     " ".join(shlex.quote(c) for c in cmd))
+    return list(ssh) + [host, remote]
+
+
+def launch(cmd, nworker, max_attempts=20, env=None, capture=False, timeout=None,
+           per_rank_gpu=False, verbose=False, host="127.0.0.1", hosts=None, ssh=("ssh", "-o", "StrictHostKeyChecking=no")):
+    """Run ``cmd`` (argv list) as ``nworker`` processes under a fresh tracker.
+
+    per_rank_gpu: export RABIT_DEVICE_ORDINAL / RABIT_LOCAL_RANK so a task uses the GPU with its index on its host.
+    hosts: None = all workers on this machine; otherwise [(host, slots)] and the workers are started through ``ssh``
+      (``host`` is then the address under which the remote workers reach the tracker).
     """
+    placement = place_tasks(hosts, nworker) if hosts else None
     tracker = Tracker(nworker, host=host, verbose=verbose).start()
     res = JobResult()
     lock = threading.Lock()
@@ -62,13 +103,20 @@ def launch(cmd, nworker, max_attempts=20, env=None, capture=False, timeout=None,
             wenv.update(tracker.worker_env())
             wenv["DMLC_TASK_ID"] = str(i)
             wenv["DMLC_NUM_ATTEMPT"] = str(attempt)
-            wenv["RABIT_LOCAL_RANK"] = str(i)
+            local = i if placement is None else placement[i][1]
+            wenv["RABIT_LOCAL_RANK"] = str(local)
             if per_rank_gpu:
-                wenv["RABIT_DEVICE_ORDINAL"] = str(i)
+                wenv["RABIT_DEVICE_ORDINAL"] = str(local)
             kw = {}
             if capture:
                 kw = dict(stdout=subprocess.PIPE, stderr=subprocess.STDOUT)
-            p = subprocess.Popen(cmd, env=wenv, **kw)
+            argv = cmd
+            if placement is not None:
+                # only what the job needs travels: the launcher's own environment stays here
+                keep = dict((k, v) for k, v in wenv.items()
+                            if k.startswith(("DMLC_", "RABIT_", "rabit_")) or (env and k in env))
+                argv = ssh_command(ssh, placement[i][0], os.getcwd(), keep, cmd)
+            p = subprocess.Popen(argv, env=wenv, **kw)
             with lock:
                 procs[i] = p
             try:
@@ -112,13 +160,21 @@ def main():
     ap.add_argument("--max-attempts", "--local-num-attempt", type=int, default=20, dest="max_attempts")
     ap.add_argument("--gpus", action="store_true", help="bind task i to GPU i")
     ap.add_argument("--timeout", type=float, default=None)
+    ap.add_argument("--cluster", choices=["local", "ssh"], default="local")
+    ap.add_argument("--host-file", help="ssh cluster: one host[:slots] per line")
+    ap.add_argument("--tracker-host", default="127.0.0.1", help="address of this machine as seen by the workers")
     ap.add_argument("command", nargs=argparse.REMAINDER)
     args = ap.parse_args()
     cmd = [c for c in args.command if c != "--"]
     if not cmd:
         ap.error("no command given")
+    hosts = None
+    if args.cluster == "ssh":
+        if not args.host_file:
+            ap.error("--cluster ssh needs --host-file")
+        hosts = read_host_file(args.host_file)
     res = launch(cmd, args.num_workers, max_attempts=args.max_attempts, timeout=args.timeout,
-                 per_rank_gpu=args.gpus, verbose=True)
+                 per_rank_gpu=args.gpus, verbose=True, host=args.tracker_host, hosts=hosts)
     if not res.ok:
         print("launcher: some workers failed: %r" % res.returncodes, file=sys.stderr)
     sys.exit(0 if res.ok else 1)
