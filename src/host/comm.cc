@@ -16,7 +16,11 @@ const int kProbeMs = 100;
 /*! \brief handshake cookie of the tracker protocol (reference allreduce_base.h kMagic) */
 const int kTrackerMagic = 0xff99;
 
+thread_local int g_last_sock_errno = 0;
+thread_local char g_last_sock_what[96] = "";
+
 Status ErrnoStatus() {
+  g_last_sock_errno = errno;
   switch (errno) {
     case ECONNRESET: case EPIPE: case ECONNABORTED: case ENOTCONN: case ETIMEDOUT:
       return Status::kPeerClosed;
@@ -32,8 +36,11 @@ Status RecvSome(Link *l, char *p, size_t max, size_t *got) {
   if (max == 0) return Status::kOk;
   ssize_t n = l->sock.Recv(p, max);
   if (n > 0) { *got = static_cast<size_t>(n); return Status::kOk; }
-  if (n == 0) return Status::kPeerClosed;
-  return WouldBlock() ? Status::kOk : ErrnoStatus();
+  if (n == 0) { snprintf(g_last_sock_what, sizeof(g_last_sock_what), "recv=0 from %d", l->rank); return Status::kPeerClosed; }
+  if (WouldBlock()) return Status::kOk;
+  snprintf(g_last_sock_what, sizeof(g_last_sock_what), "recv(%p,%lu) from %d", static_cast<void *>(p),
+           static_cast<unsigned long>(max), l->rank);  // NOLINT(*)
+  return ErrnoStatus();
 }
 /*! \brief one non-blocking send */
 Status SendSome(Link *l, const char *p, size_t max, size_t *put) {
@@ -41,11 +48,17 @@ Status SendSome(Link *l, const char *p, size_t max, size_t *put) {
   if (max == 0) return Status::kOk;
   ssize_t n = l->sock.Send(p, max);
   if (n >= 0) { *put = static_cast<size_t>(n); return Status::kOk; }
-  return WouldBlock() ? Status::kOk : ErrnoStatus();
+  if (WouldBlock()) return Status::kOk;
+  snprintf(g_last_sock_what, sizeof(g_last_sock_what), "send(%p,%lu) to %d", static_cast<const void *>(p),
+           static_cast<unsigned long>(max), l->rank);  // NOLINT(*)
+  return ErrnoStatus();
 }
 /*! \brief largest multiple of unit that is <= v (at least one unit) */
 inline size_t FloorTo(size_t v, size_t unit) { return std::max(unit, v / unit * unit); }
 }  // namespace
+
+int LastSocketErrno() { return g_last_sock_errno; }
+const char *LastSocketWhat() { return g_last_sock_what; }
 
 const char *StatusName(Status s) {
   switch (s) {

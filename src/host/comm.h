@@ -35,6 +35,9 @@ enum class Status {
 };
 inline bool Ok(Status s) { return s == Status::kOk; }
 const char *StatusName(Status s);
+/*! \brief errno behind the most recent kSockError / kPeerClosed of this thread (diagnostics) */
+int LastSocketErrno();
+const char *LastSocketWhat();
 
 /*! \brief one established peer connection */
 struct Link {

@@ -278,6 +278,9 @@ int RobustEngine::LoadCheckPoint(Serializable *global_model, Serializable *local
     // every rank is asking: nothing exists yet
     if (comm_.cfg.debug) utils::HandleLogInfo("[%d] loadcheckpoint reset\n", comm_.rank);
     results_.Clear(); seq_ = 0; version_number_ = 0;
+    // nothing of an earlier attempt may survive a fresh start (e.g. a checkpoint transfer that broke half-way)
+    global_blob_.clear(); lazy_model_ = nullptr;
+    for (int g = 0; g < 2; ++g) { local_[g].clear(); local_has_[g].clear(); }
     return 0;
   }
   std::vector<std::string> &slot = local_[local_gen_];

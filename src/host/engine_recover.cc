@@ -106,18 +106,30 @@ Status RobustEngine::ServeLoad(bool requester) {
   size_t size = 0; bool any = false;
   for (int r = 0; r < n; ++r) {
     has[r] = tab[r * 3] != 0; need[r] = tab[r * 3 + 1] != 0;
-    if (has[r]) { any = true; size = tab[r * 3 + 2]; }
+    if (!has[r]) continue;
+    // every holder sends `size` bytes out of its own copy: they had better be the same blob
+    utils::Check(!any || size == tab[r * 3 + 2], "[%d] LoadCheckPoint: holders disagree on the checkpoint size "
+                 "(%lu vs %lu bytes)", comm_.rank, static_cast<unsigned long>(size),  // NOLINT(*)
+                 static_cast<unsigned long>(tab[r * 3 + 2]));                          // NOLINT(*)
+    any = true; size = tab[r * 3 + 2];
   }
   utils::Check(any, "[%d] LoadCheckPoint: no surviving rank holds the global checkpoint", comm_.rank);
-  if (requester) global_blob_.resize(size);
-  if (size == 0) return Status::kOk;  // nothing committed yet: version 0
-  {
-    Status dst = Status::kOk;
-    if (DeviceDeliver(has, need, holder ? global_blob_.data() : nullptr, nullptr,
-                      requester ? &global_blob_[0] : nullptr, size, &dst)) return dst;
+  if (size == 0) {  // nothing committed yet: version 0
+    if (requester) global_blob_.clear();
+    return Status::kOk;
   }
-  void *p = (requester || holder) ? &global_blob_[0] : nullptr;
-  return RingDeliver(has, need, p, size);
+  // A requester installs the blob only once all of it has arrived: a transfer that breaks half-way must not
+  // leave a torn checkpoint behind (this rank may be asked to serve "its" checkpoint a moment later).
+  std::string incoming;
+  if (requester) incoming.resize(size);
+  Status dst = Status::kOk;
+  if (!DeviceDeliver(has, need, holder ? global_blob_.data() : nullptr, nullptr, requester ? &incoming[0] : nullptr,
+                     size, &dst)) {
+    void *p = requester ? static_cast<void *>(&incoming[0]) : (holder ? static_cast<void *>(&global_blob_[0]) : nullptr);
+    dst = RingDeliver(has, need, p, size);
+  }
+  if (Ok(dst) && requester) global_blob_.swap(incoming);
+  return dst;
 }
 
 // bootstrap cache wire form: u64 n, then n x (u64 klen, key, u64 vlen, value)

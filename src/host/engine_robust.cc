@@ -115,8 +115,8 @@ bool RobustEngine::Healthy(Status s) {
   ++recover_counter_;
   in_sync_ = false;
   if (comm_.cfg.debug) {
-    utils::HandleLogInfo("[%d] link failure (%s) at version %d seq %d, re-joining\n", comm_.rank,
-                         StatusName(s), version_number_, seq_);
+    utils::HandleLogInfo("[%d] link failure (%s, errno %d, %s) at version %d seq %d, re-joining\n", comm_.rank,
+                         StatusName(s), LastSocketErrno(), LastSocketWhat(), version_number_, seq_);
   }
   StartWatchdog();
   // Drop EVERY link: neighbours observe it as a failure too and the whole job funnels into the

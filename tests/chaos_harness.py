@@ -16,7 +16,7 @@ sys.path.insert(0, ROOT)
 from rabit_b200.parallel.tracker import Tracker  # noqa: E402
 
 
-def run(seed, programs=("model_recover", "model_recover", "lazy_recover"), timeout=120):
+def run(seed, programs=("model_recover", "model_recover", "lazy_recover"), timeout=120, extra_args=(), tail=700):
     rng = random.Random(seed)
     world = rng.choice([2, 3, 4, 6, 8])
     prog = rng.choice(list(programs))
@@ -29,6 +29,7 @@ def run(seed, programs=("model_recover", "model_recover", "lazy_recover"), timeo
         args.append("rabit_bootstrap_cache=1")
     if rng.random() < 0.5:
         args.append("rabit_reduce_ring_mincount=1")
+    args += list(extra_args)
     tracker = Tracker(world).start()
     procs, outs, attempts, done = {}, {i: b"" for i in range(world)}, {i: 0 for i in range(world)}, {}
 
@@ -79,7 +80,7 @@ def run(seed, programs=("model_recover", "model_recover", "lazy_recover"), timeo
             pass
     tracker.close()
     return ok, dict(seed=seed, world=world, prog=prog, args=args, kills=kills, done=done,
-                    tails={i: outs[i].decode(errors="replace")[-700:] for i in range(world)})
+                    tails={i: outs[i].decode(errors="replace")[-tail:] for i in range(world)})
 
 
 if __name__ == "__main__":
