@@ -39,17 +39,28 @@ Status RobustEngine::ServeResult(void *buf, size_t size, uint32_t seq, bool requ
                  "in current VersionNumber (rank %d expects %lu bytes, cached %lu)", r,
                  static_cast<unsigned long>(tab[r * 3 + 2]), static_cast<unsigned long>(held_size));  // NOLINT(*)
   }
+  // A requester lands the bytes next to its buffer and takes them over only when all of them are there. Its buffer
+  // still holds its own INPUT for this op: if the last holder dies half-way and comes back without the result, the
+  // op is executed again by everybody, from that input. (The reference receives straight into the caller's buffer,
+  // allreduce_robust.cc:1103-1140, and would then reduce a half-overwritten buffer.)
+  HostBytes landing;
+  if (requester) landing.resize(held_size);
+  Status dst = Status::kOk;
   {
-    Status dst = Status::kOk;
     const void *src_dev = held != nullptr ? held->dev : nullptr;
     const void *src_host = (held != nullptr && held->dev == nullptr) ? held->host.data() : nullptr;
-    if (DeviceDeliver(has, need, src_host, src_dev, requester ? buf : nullptr, held_size, &dst)) return dst;
+    if (DeviceDeliver(has, need, src_host, src_dev, requester ? landing.data() : nullptr, held_size, &dst)) {
+      if (Ok(dst) && requester && held_size != 0) std::memcpy(buf, landing.data(), held_size);
+      return dst;
+    }
   }
   // only a holder whose successor actually pulls pays for a device->host copy of the entry
-  void *p = requester ? buf : nullptr;
+  void *p = requester ? landing.data() : nullptr;
   if (held != nullptr && !has[(comm_.rank + 1) % n]) p = results_.HostView(held);
   if (held != nullptr && p == nullptr) return Status::kOk;
-  return RingDeliver(has, need, p, held_size);
+  dst = RingDeliver(has, need, p, held_size);
+  if (Ok(dst) && requester && held_size != 0) std::memcpy(buf, landing.data(), held_size);
+  return dst;
 }
 
 bool RobustEngine::DeviceDeliver(const std::vector<char> &has, const std::vector<char> &need,

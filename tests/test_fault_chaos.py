@@ -6,7 +6,7 @@ import pytest
 from chaos_harness import run
 
 
-@pytest.mark.parametrize("seed", [3, 11, 261, 393, 1007, 1042])
+@pytest.mark.parametrize("seed", [3, 11, 261, 393, 1007, 1042, 2043, 4219, 8559])
 def test_random_sigkills(built, seed):
     ok, info = run(seed)
     assert ok, {k: info[k] for k in ("prog", "world", "args", "kills", "done", "tails")}
