@@ -38,7 +38,8 @@ def run(seed, programs=("model_recover", "model_recover", "lazy_recover"), timeo
         env.update(tracker.worker_env())
         env["DMLC_TASK_ID"] = str(i)
         env["DMLC_NUM_ATTEMPT"] = str(attempts[i])
-        procs[i] = subprocess.Popen([os.path.join(ROOT, "build", "bin", prog)] + args, env=env,
+        bindir = os.environ.get("RABIT_CHAOS_BIN", os.path.join(ROOT, "build", "bin"))   # e.g. build/san_address
+        procs[i] = subprocess.Popen([os.path.join(bindir, prog)] + args, env=env,
                                     stdout=subprocess.PIPE, stderr=subprocess.STDOUT)
 
     for i in range(world):
