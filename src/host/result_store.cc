@@ -75,7 +75,9 @@ void HostBytes::resize(size_t n) {
     }
   }
   void *fresh = nullptr;
-  if (n >= kPoolMinBlock && n < 2 * kHuge && (p_ = Pool().Carve(n)) != nullptr) {
+  // (slab memory is never returned to the system: once a lot of it sits idle in sizes nobody asks for any more,
+  // stop carving and let malloc / free handle the odd sizes)
+  if (n >= kPoolMinBlock && n < 2 * kHuge && Pool().idle_bytes <= kPoolMaxBytes && (p_ = Pool().Carve(n)) != nullptr) {
     size_ = n; cap_ = (n + 255) & ~static_cast<size_t>(255);
     return;
   }
