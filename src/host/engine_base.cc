@@ -52,7 +52,10 @@ bool BaseEngine::Init(int argc, char *argv[]) {
       fprintf(stderr, "[rabit] the job finished while this worker was being restarted; nothing to re-join, exit 0\n");
       exit(0);
     }
-    return false;
+    // Carrying on would mean running as a silent world of one next to a job that is waiting for this rank: stop
+    // here, the launcher starts the worker again (the reference throws from its tracker connect as well).
+    utils::Error("cannot join the job: the rendezvous through tracker %s:%d failed", comm_.cfg.tracker_uri.c_str(),
+                 comm_.cfg.tracker_port);
   }
   if (comm_.world > 1 || comm_.cfg.device_force) {
     device_.reset(DeviceBackend::Create(comm_.cfg));
