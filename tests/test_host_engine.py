@@ -121,3 +121,12 @@ def test_watchdog_kills_stuck_survivors():
     # which task holds rank 1 depends on arrival order at the tracker: one abort, two watchdog exits
     assert sorted(res.returncodes.values()) == [-6, 10, 10]
     assert any("exit due to time out 2 s" in o for o in res.outputs.values())
+
+
+def test_recovery_at_world_31(built):
+    """the reference's sweep goes up to 31 machines (test/speed_runner.py:13-18): ring + tree + recovery at that size"""
+    res = run_job([bin_path("model_recover"), "10000", "mock=0,0,1,0", "mock=1,1,1,0", "mock=9,1,1,0", "mock=15,2,3,0",
+                   "rabit_bootstrap_cache=1", "rabit_timeout=1", "rabit_timeout_sec=100"], 31, timeout=240)
+    assert res.ok, {i: o[-400:] for i, o in res.outputs.items() if "iter 2" not in o}
+    assert res.restarts == 4
+    assert all("iter 2 checkpointed (version 3)" in o for o in res.outputs.values())
