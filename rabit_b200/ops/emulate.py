@@ -39,6 +39,11 @@ def load_library():
                                        c.POINTER(c.c_int)]
     lib.RabitEmuCollective.restype = c.c_int
     lib.RabitDeviceLaunchCount.restype = c.c_ulonglong
+    lib.RabitEmuStreamAllreduce.argtypes = [c.c_int, c.POINTER(c.c_void_p), c.POINTER(c.c_void_p), c.c_size_t, c.c_int,
+                                            c.c_int, c.c_size_t, c.c_int, c.c_int, c.POINTER(c.c_int)]
+    lib.RabitEmuStreamAllreduce.restype = c.c_int
+    lib.RabitEmuSetEpoch.argtypes = [c.c_int, c.c_size_t, c.c_uint]
+    lib.RabitEmuSetEpoch.restype = c.c_int
     _lib_cache = lib
     return lib
 
@@ -75,6 +80,34 @@ def collective(kind, bufs, algo=ONESHOT, op=2, root=0, keeps=None, slices=None, 
     if rc != 0:
         raise RuntimeError("RabitEmuCollective failed with %d" % rc)
     return list(status)
+
+
+def stream_allreduce(bufs, op=2, keeps=None, chunk_bytes=1 << 20, fail_chunk=-1, blocks=0):
+    """The chunked (streamed) allreduce over ``bufs``: every chunk is copied into the emulated rank's stage
+    and reduced by one launch of the StreamP2P kernel.  ``fail_chunk`` >= 0 injects a consensus mismatch in
+    that chunk; the call then undoes the op from the stage copy like the multi-GPU path does.
+
+    Returns the per-rank status of the op (0 ok, 1 mismatch, 2 timeout).
+    """
+    lib = load_library()
+    n = len(bufs)
+    t0 = bufs[0]
+    for t in bufs:
+        assert t.is_cuda and t.is_contiguous() and t.dtype == t0.dtype
+    status = (ctypes.c_int * n)()
+    torch.cuda.synchronize()
+    rc = lib.RabitEmuStreamAllreduce(n, _ptrs(bufs), _ptrs(keeps) if keeps is not None else None, t0.numel(),
+                                     _TORCH_DTYPE[t0.dtype], op, chunk_bytes, fail_chunk, blocks, status)
+    if rc != 0:
+        raise RuntimeError("RabitEmuStreamAllreduce failed with %d" % rc)
+    return list(status)
+
+
+def set_epoch(nranks, payload_bytes, epoch):
+    """Test hook: move the op counter of the emulated ranks to ``epoch`` (flag rows made consistent with it)."""
+    rc = load_library().RabitEmuSetEpoch(nranks, payload_bytes, epoch & 0xFFFFFFFF)
+    if rc != 0:
+        raise RuntimeError("RabitEmuSetEpoch failed with %d" % rc)
 
 
 def launch_count():

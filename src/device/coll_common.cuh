@@ -77,6 +77,7 @@ struct Params {
   unsigned long long timeout_ns;
   unsigned long long *trace;  // optional host-mapped phase timestamps of block 0 (NULL = off)
   int device_epoch;           // 1: take the op epoch from Control::epoch_dev instead of `epoch` (graph-replayable)
+  int chained;                // 1: not the first kernel of a multi-kernel op: leave at once if an earlier one failed
 };
 
 /*! \brief the op epoch of the running kernel. With device_epoch it was fetched from the control block by BeginOp
@@ -152,7 +153,8 @@ __device__ __forceinline__ int FlagBarrier(const Params &p, int me, RowOf row_of
     unsigned int spins = 0;
     while (true) {
       seen = LoadAcquireSys(slot);
-      if (static_cast<unsigned int>(seen >> 32) >= seq) break;
+      // wrap-safe "seen >= seq": the 32-bit op counter may roll over in a long graph-replay loop
+      if (static_cast<int>(static_cast<unsigned int>(seen >> 32) - seq) >= 0) break;
       if ((++spins & 0x3ff) == 0) {
         if (*p.abort_flag != 0) { verdict = kStAborted; break; }
         if (GlobalTimer() > deadline) { verdict = kStTimeout; break; }
@@ -191,7 +193,9 @@ __device__ __forceinline__ int CommitGate(const Params &p, int me, int verdict, 
   if (p.keep[p.emulate ? me : 0] == nullptr || gridDim.x == 1) return verdict;
   __syncthreads();
   Control *c = CtrlOf(p, me);
-  const unsigned long long tag = static_cast<unsigned long long>(OpEpoch(p) + 1) << 32;
+  // slot word = op epoch | "posted" marker | verdict: zeroed memory never looks posted, whatever the epoch
+  const unsigned long long kMark = 0x80000000ull;
+  const unsigned long long tag = (static_cast<unsigned long long>(OpEpoch(p)) << 32) | kMark;
   const int t = threadIdx.x;
   if (t == 0) {
     *s_verdict = verdict;
@@ -210,7 +214,7 @@ __device__ __forceinline__ int CommitGate(const Params &p, int me, int verdict, 
         while (true) {
           unsigned long long v;
           asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(&c->gate_slot[b]) : "memory");
-          if ((v >> 32) == (tag >> 32)) { if (static_cast<unsigned int>(v) != 0u) seen = kStAborted; break; }
+          if ((v & ~(kMark - 1)) == tag) { if ((v & (kMark - 1)) != 0u) seen = kStAborted; break; }
           if ((++spins & 0x3ff) == 0) {
             if (*p.abort_flag != 0) { seen = kStAborted; break; }
             if (GlobalTimer() > deadline) { seen = kStTimeout; break; }
@@ -229,7 +233,7 @@ __device__ __forceinline__ int CommitGate(const Params &p, int me, int verdict, 
     while (true) {
       unsigned long long v;
       asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(&c->gate_go) : "memory");
-      if ((v >> 32) == (tag >> 32)) { if (static_cast<unsigned int>(v) != 0u) seen = kStAborted; break; }
+      if ((v & ~(kMark - 1)) == tag) { if ((v & (kMark - 1)) != 0u) seen = kStAborted; break; }
       if ((++spins & 0x3ff) == 0) {
         if (*p.abort_flag != 0) { seen = kStAborted; break; }
         if (GlobalTimer() > deadline) { seen = kStTimeout; break; }
@@ -262,6 +266,17 @@ __device__ __forceinline__ void EndOp(const Params &p, int me) {
       *reinterpret_cast<volatile unsigned int *>(&c->epoch_dev) = OpEpoch(p) + 1;
     }
   }
+}
+
+/*! \brief true when an earlier kernel of the same multi-kernel op already reported a failure (block-uniform).
+ *  After a failed chunk the peers may have left for the host protocol (consensus mismatch), so the remaining
+ *  kernels of the op must not wait for them. Reads the host-mapped status word: chained kernels only. */
+__device__ __forceinline__ bool Poisoned(const Params &p, int me) {
+  __shared__ int s_poison;
+  if (!p.chained) return false;
+  if (threadIdx.x == 0) s_poison = *reinterpret_cast<volatile int *>(p.status + (p.emulate ? me : 0));
+  __syncthreads();
+  return s_poison != 0;
 }
 
 /*! \brief phase timestamp (block 0 / thread 0 only) for the tuning tools; no-op unless enabled */

@@ -112,7 +112,7 @@ template <typename T, typename OP>
 __global__ void __launch_bounds__(512) TwoShotInPlace(Params p) {
   const int me = p.emulate ? blockIdx.y : p.rank;
   BeginOp(p, me);
-  TwoShotInPlaceBody<T, OP>(p);
+  if (!Poisoned(p, me)) TwoShotInPlaceBody<T, OP>(p);
   EndOp(p, me);
 }
 
@@ -170,7 +170,7 @@ template <typename MM>
 __global__ void __launch_bounds__(512) NvlsInPlace(Params p) {
   const int me = p.emulate ? blockIdx.y : p.rank;
   BeginOp(p, me);
-  NvlsInPlaceBody<MM>(p);
+  if (!Poisoned(p, me)) NvlsInPlaceBody<MM>(p);
   EndOp(p, me);
 }
 

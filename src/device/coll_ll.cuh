@@ -65,7 +65,8 @@ __device__ __forceinline__ void OneShotLLBody(const Params &p) {
   const int n = p.world;
   unsigned int *user = static_cast<unsigned int *>(p.user[ix]);
   unsigned int *keep = static_cast<unsigned int *>(p.keep[ix]);
-  const unsigned int tag = OpEpoch(p) + 1;
+  // never 0 (zeroed or never-written slot words must not look tagged), distinct for the two ops that share a parity
+  const unsigned int tag = (OpEpoch(p) & 0x7fffffffu) + 1;
   const unsigned int words = static_cast<unsigned int>(p.bytes / 4);
   constexpr unsigned int kUnitWords = sizeof(T) > 4 ? 2 : 1;   // an element never straddles two threads
   const unsigned int units = words / kUnitWords;
@@ -102,7 +103,7 @@ __device__ __forceinline__ void OneShotLLBody(const Params &p) {
   // thread at most ONE unit, so the result waits in registers until the whole grid is known to be complete.
   const unsigned int u = u_begin + threadIdx.x;
   const bool mine = u < u_end;
-  unsigned int acc[kUnitWords], in[kUnitWords];
+  alignas(8) unsigned int acc[kUnitWords], in[kUnitWords];  // reinterpreted as (up to) 8-byte T below
   if (mine) {
     bool ok = true;
     for (int q = 0; q < n && ok; ++q) {

@@ -20,18 +20,19 @@
 #include <algorithm>
 #include <chrono>
 #include <cstdio>
+#include <cstddef>
 #include <cstring>
 #include <map>
 #include <string>
 #include <thread>
+#include <utility>
 #include <vector>
 
 #include "coll_kernels.cuh"
 #include "coll_tma.cuh"
 #include "coll_nvls.cuh"
-#include "coll_pipe.cuh"
 #include "coll_inplace.cuh"
-#include "coll_rounds.cuh"
+#include "coll_stream.cuh"
 #include "coll_ll.cuh"
 #include "device_backend.h"
 #include "../host/engine_core.h"

@@ -25,6 +25,7 @@ struct DeviceStats {
   uint64_t fused_consensus_ok = 0;
   uint64_t fused_consensus_mismatch = 0;
   uint64_t timeouts = 0;
+  uint64_t streamed_ops = 0;      // allreduces that ran as chunked, copy-engine fed ops
   int nvls = 0;                   // multicast path usable
   int p2p = 0;                    // peer mappings established
 };
@@ -62,8 +63,22 @@ class DeviceBackend {
    *   that copy is the rabit result cache entry, fused into the kernel's epilogue
    */
   virtual Status Allreduce(void *dptr, size_t count, int dtype, int op, int lanes,
-                           uint32_t code, void *keep) = 0;
-  virtual Status Broadcast(void *dptr, size_t size, int root, uint32_t code, void *keep) = 0;
+                           uint32_t code, void *keep, int flags = 0) = 0;
+  /*! \brief flags of Allreduce / Broadcast */
+  enum {
+    /*! \brief pick the kernel from rank-uniform values only (no zero-copy, no alignment-dependent variant):
+     *  set by the engine after a kernel reported a consensus mismatch although every rank is at this very op,
+     *  i.e. the ranks passed differently placed or aligned buffers */
+    kOpConservative = 1
+  };
+  /*! \brief largest allreduce (bytes) that can run as ONE recoverable op right now, after trying to make room
+   *  for `want` bytes (collective: may re-allocate and re-exchange the arena). HOST buffers count too. */
+  virtual size_t MaxOpBytes(size_t want) = 0;
+  /*! \brief op counters of the flag protocols; the engines keep them equal on all ranks (consensus envelope) */
+  virtual uint32_t OpEpoch() = 0;
+  virtual uint64_t OpRounds() const = 0;
+  virtual void AdoptEpoch(uint32_t epoch, uint64_t rounds) = 0;
+  virtual Status Broadcast(void *dptr, size_t size, int root, uint32_t code, void *keep, int flags = 0) = 0;
   virtual Status Allgather(void *dptr, size_t total, size_t slice_begin, size_t slice_end,
                            uint32_t code, void *keep) = 0;
 

@@ -59,15 +59,19 @@ struct Config {
   size_t device_arena = 0;                   // bytes of symmetric staging; 0 = grow on demand
   size_t device_heap = 0;                    // bytes of symmetric heap for zero-copy buffers (RabitDeviceSymAlloc)
   size_t device_oneshot_max = 512 << 10;     // bytes: <= -> one-shot kernel
-  size_t device_pipe_min = 8 << 20;          // bytes: >= -> pipelined (warp-specialised) two-shot
-  size_t device_nvls_min = 64 << 10;         // bytes: >= -> multimem kernel when available
+  size_t device_nvls_min = 0;                // bytes: >= -> multimem kernel when available; 0 = table by world size
+  size_t device_ll_max = 0;                  // bytes: <= -> tagged-word kernel; 0 = table by world size
+  size_t device_stream_min = 0;              // bytes: >= -> chunked, copy-engine fed allreduce; 0 = table (32 MiB)
+  size_t device_stream_chunk = 0;            // bytes per chunk of that path; 0 = table (64 MiB)
+  size_t device_stream_first = 0;            // bytes of its first chunk; 0 = table (8 MiB)
+  std::string device_tune = "";              // file with measured thresholds (benchmarks/algo_sweep.py --emit-table)
   int device_blocks = 0;                     // 0 = table default
   int device_timeout_ms = 20000;             // bounded spin before a peer is declared dead
   std::string device_algo = "auto";          // auto|oneshot|twoshot|tma|nvls
   bool device_force = false;                 // run kernels even at world size 1
   size_t device_cache_bytes = 16UL << 30;    // device-resident result cache budget
-  size_t device_host_min = 0;                // bytes: HOST buffers >= this ride PCIe + NVLink instead of TCP; 0 = off
-  size_t device_host_chunk = 16UL << 20;     // pipeline granule of that path (H2D | kernel | D2H overlap)
+  size_t device_host_min = 4UL << 20;        // bytes: HOST buffers >= this ride PCIe + NVLink instead of TCP; 0 = off
+  size_t device_host_chunk = 32UL << 20;     // pipeline granule of that path (H2D | kernel | D2H overlap)
 
   /*! \brief names looked up in the environment at Init */
   static const std::vector<std::string> &EnvNames() {
@@ -79,7 +83,8 @@ struct Config {
       "rabit_reduce_ring_mincount", "rabit_tree_reduce_minsize", "rabit_reduce_buffer",
       "rabit_engine", "rabit_device", "rabit_device_arena", "rabit_device_algo",
       "rabit_device_blocks", "rabit_device_timeout_ms", "rabit_device_force",
-      "rabit_device_oneshot_max", "rabit_device_nvls_min", "rabit_device_pipe_min", "rabit_device_heap", "rabit_device_cache",
+      "rabit_device_oneshot_max", "rabit_device_nvls_min", "rabit_device_ll_max", "rabit_device_heap", "rabit_device_cache",
+      "rabit_device_stream_min", "rabit_device_stream_chunk", "rabit_device_stream_first", "rabit_device_tune",
       "rabit_device_host_min", "rabit_device_host_chunk",
       "rabit_world_size", "rabit_slave_port"};
     return names;
@@ -142,7 +147,11 @@ struct Config {
     else if (is("rabit_device_arena")) device_arena = ParseBytes(name, val);
     else if (is("rabit_device_heap")) device_heap = ParseBytes(name, val);
     else if (is("rabit_device_oneshot_max")) device_oneshot_max = ParseBytes(name, val);
-    else if (is("rabit_device_pipe_min")) device_pipe_min = ParseBytes(name, val);
+    else if (is("rabit_device_ll_max")) device_ll_max = ParseBytes(name, val);
+    else if (is("rabit_device_stream_min")) device_stream_min = ParseBytes(name, val);
+    else if (is("rabit_device_stream_chunk")) device_stream_chunk = ParseBytes(name, val);
+    else if (is("rabit_device_stream_first")) device_stream_first = ParseBytes(name, val);
+    else if (is("rabit_device_tune")) device_tune = val;
     else if (is("rabit_device_nvls_min")) device_nvls_min = ParseBytes(name, val);
     else if (is("rabit_device_cache")) device_cache_bytes = ParseBytes(name, val);
     else if (is("rabit_device_host_min")) device_host_min = ParseBytes(name, val);

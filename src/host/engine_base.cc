@@ -59,13 +59,41 @@ bool BaseEngine::Init(int argc, char *argv[]) {
   }
   if (comm_.world > 1 || comm_.cfg.device_force) {
     device_.reset(DeviceBackend::Create(comm_.cfg));
-    if (device_ && !device_->Attach(&comm_)) {
-      utils::Check(comm_.cfg.device != "on", "rabit_device=on but the device arena could not be set up");
-      device_.reset();
-    }
+    // (a link that breaks this early is fatal here; the robust engine re-joins instead, see RobustEngine::Init)
+    utils::Check(this->AttachDevice() != AttachResult::kLinkError, "lost a peer while setting up the device arena");
   }
   initialized_ = true;
   return true;
+}
+
+BaseEngine::AttachResult BaseEngine::AttachDevice() {
+  // Whether the job uses the NVLink arena is ONE decision of all ranks. A rank without a usable GPU (none
+  // visible, wrong architecture, rabit_device=off only there) must not skip the bootstrap while the others run
+  // its host collectives: the byte streams of different collectives would be paired. So everybody takes part in
+  // this agreement, with or without a backend, after every rendezvous.
+  int have = device_ ? 1 : 0;
+  if (comm_.world > 1) {
+    const Status st = comm_.Allreduce(&have, sizeof(int), 1, [](const void *s, void *d, int n, const MPI::Datatype &) {
+      const int *src = static_cast<const int *>(s);
+      int *dst = static_cast<int *>(d);
+      for (int i = 0; i < n; ++i) dst[i] = std::min(dst[i], src[i]);
+    });
+    if (!Ok(st)) return AttachResult::kLinkError;
+  }
+  if (have == 0) {
+    if (device_) {
+      utils::Check(comm_.cfg.device != "on", "rabit_device=on but another rank has no usable GPU");
+      if (comm_.rank == 0) fprintf(stderr, "[rabit] a rank has no usable GPU: device buffers are staged through the TCP collectives\n");
+      device_.reset();
+    }
+    return AttachResult::kNoDevice;
+  }
+  if (device_->Attach(&comm_)) return AttachResult::kAttached;
+  if (comm_.LinksBroken()) return AttachResult::kLinkError;
+  // declined by all ranks alike (several hosts, no peer access ...): the same answer everywhere
+  utils::Check(comm_.cfg.device != "on", "rabit_device=on but the device arena could not be set up");
+  device_.reset();
+  return AttachResult::kNoDevice;
 }
 
 bool BaseEngine::Shutdown(void) {

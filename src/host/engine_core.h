@@ -105,6 +105,10 @@ class BaseEngine : public IEngine {
   DeviceBackend *device() { return device_.get(); }
   /*! \brief classify a user pointer (host unless CUDA says otherwise) */
   MemKind Classify(const void *ptr) const;
+  /*! \brief outcome of the collective device bootstrap that follows every rendezvous */
+  enum class AttachResult { kAttached, kNoDevice, kLinkError };
+  /*! \brief agree with all ranks on using the device backend, then build the arena (or drop it everywhere) */
+  AttachResult AttachDevice();
 
  protected:
   /*! \brief Hadoop streaming status line (reference allreduce_base.h:248-253) */
@@ -246,11 +250,8 @@ class RobustEngine : public BaseEngine {
     std::string key;
   };
   void RunOp(OpArgs *a);
-  /*! \brief called before every chunk op after the first of a chunked host-buffer allreduce (fault injection point) */
-  virtual void BetweenChunks() {}
-  /*! \brief large host buffers: chunked H2D | device collective | D2H pipeline (engine_ops.cc); false = not taken */
-  bool HostViaDevice(void *buf, size_t type_nbytes, size_t count, ReduceFunction reducer, int dtype, int op,
-                     const std::string &key);
+  /*! \brief does this allreduce on a HOST buffer go through the device kernels (H2D | kernel | D2H)? */
+  bool HostOverDevice(const OpArgs &a) const;
   Status TryOp(const OpArgs &a, char *slot, const char *input);
 
   /*!
@@ -264,6 +265,7 @@ class RobustEngine : public BaseEngine {
   bool Healthy(Status s);
   void StartWatchdog();
   void StopWatchdog();
+  void Rejoin();
 
   // ---- data movers run by every rank once Decide() says so ----
   Status ServeResult(void *buf, size_t size, uint32_t seq, bool requester);
@@ -336,7 +338,6 @@ class MockEngine : public RobustEngine {
  private:
   /*! \brief die here if (rank, version, seq, trial) was scripted */
   void Verify(const char *what);
-  void BetweenChunks() override { Verify("AllReduce chunk"); }
   double tsum_allreduce_ = 0.0, tsum_allgather_ = 0.0, time_checkpoint_ = 0.0;
 };
 

@@ -38,7 +38,9 @@ Status RobustEngine::TryOp(const OpArgs &a, char *slot, const char *input) {
 
 void RobustEngine::RunOp(OpArgs *a) {
   const bool on_device = Classify(a->buf) == MemKind::kDevice;
-  if (comm_.world <= 1 && !(on_device && device_ && comm_.cfg.device_force)) {
+  // a large typed allreduce on a HOST buffer rides PCIe + NVLink through the same kernels (HostOverDevice)
+  const bool host_fused = !on_device && HostOverDevice(*a);
+  if (comm_.world <= 1 && !((on_device || host_fused) && device_ && comm_.cfg.device_force)) {
     if (a->prepare_fun != nullptr) a->prepare_fun(a->prepare_arg);
     return;
   }
@@ -55,7 +57,7 @@ void RobustEngine::RunOp(OpArgs *a) {
   const uint32_t flags = boot ? proto::kLoadCache : 0;
 
   // device buffers whose op the kernels cannot express go through a host mirror
-  const bool fused = on_device && device_ != nullptr &&
+  const bool fused = (on_device || host_fused) && device_ != nullptr && device_->attached() &&
                      (a->kind != OpKind::kAllreduce || (a->dtype >= 0 && a->op >= 0));
   // (allocated only when the host protocol actually has to look at the bytes)
   std::string mirror;
@@ -80,6 +82,11 @@ void RobustEngine::RunOp(OpArgs *a) {
   char *slot = nullptr;
   bool dropped = false;
   const bool use_kernel = fused && !boot;
+  // set once a kernel has reported a mismatch although the host protocol says that every rank is at this very
+  // op: the ranks chose different kernels (differently aligned / placed buffers), so take the variant that
+  // depends on nothing but the op itself
+  int dev_flags = 0;
+  bool mismatched = false;
   while (true) {
     if (use_kernel && in_sync_) {
       // Fast path: ONE kernel does consensus + transfer + reduce + the cache copy. It is only
@@ -91,9 +98,9 @@ void RobustEngine::RunOp(OpArgs *a) {
       Status st = Status::kOk;
       switch (a->kind) {
         case OpKind::kAllreduce:
-          st = device_->Allreduce(a->buf, a->bytes / DTypeBytes(a->dtype), a->dtype, a->op, 1, code, keep);
+          st = device_->Allreduce(a->buf, a->bytes / DTypeBytes(a->dtype), a->dtype, a->op, 1, code, keep, dev_flags);
           break;
-        case OpKind::kBroadcast: st = device_->Broadcast(a->buf, a->bytes, a->root, code, keep); break;
+        case OpKind::kBroadcast: st = device_->Broadcast(a->buf, a->bytes, a->root, code, keep, dev_flags); break;
         case OpKind::kAllgather:
           st = device_->Allgather(a->buf, a->bytes, a->slice_begin, a->slice_end, code, keep);
           break;
@@ -108,6 +115,7 @@ void RobustEngine::RunOp(OpArgs *a) {
       // kMismatch: somebody is elsewhere in the protocol. Anything else: a peer is gone, tear down
       // and re-join. Either way the host protocol decides what happens next.
       if (st != Status::kMismatch) Healthy(st);
+      else mismatched = true;
     }
     const std::function<void *()> lazy = [&]() -> void * { need_view(); return view; };
     // tiny host allreduces without a lazy prepare ride along with the consensus round itself
@@ -131,6 +139,7 @@ void RobustEngine::RunOp(OpArgs *a) {
       break;
     }
     in_sync_ = true;  // the consensus round just said: every rank is about to run this very op
+    if (mismatched) dev_flags |= DeviceBackend::kOpConservative;
     if (inl.done) {
       // the result came back with the consensus round: cache it like any other
       slot = results_.AllocTemp(a->bytes);
@@ -173,63 +182,53 @@ void RobustEngine::RunOp(OpArgs *a) {
 
 /*!
  * A large HOST buffer rides PCIe + NVLink instead of the TCP links (no counterpart in the reference, whose
- * only transport is the socket ring of allreduce_base.cc:857-977). The buffer is cut into chunks; every chunk
- * is an ordinary sequence-numbered device-pointer op (fused kernel, result cached on the device, recoverable
- * like any other), and the copies of neighbouring chunks overlap it: H2D(i+1..) | kernel(i) | D2H(i-1).
- * A chunk's result is copied back only after its own op has succeeded, so after a failure the host buffer
- * holds finished chunks and untouched inputs, never garbage; a restarted rank replays the same chunk ops.
- * All ranks derive the same chunking from the same parameters.
+ * only transport is the socket ring of allreduce_base.cc:857-977). It is ONE sequence-numbered op: the device
+ * backend cuts it into chunks and overlaps H2D(i+1) | kernel(i) | D2H(i-1) on copy engines; the stage copy
+ * of the input is the backup that makes the op all-or-nothing (device_backend_stream.inc).
+ * The decision uses only values that are the same on every rank.
  */
-bool RobustEngine::HostViaDevice(void *buf, size_t type_nbytes, size_t count, ReduceFunction reducer, int dtype,
-                                 int op, const std::string &key) {
-  const size_t bytes = type_nbytes * count;
+bool RobustEngine::HostOverDevice(const OpArgs &a) const {
   const Config &cfg = comm_.cfg;
-  if (device_ == nullptr || !device_->attached() || cfg.device_host_min == 0 || bytes < cfg.device_host_min) return false;
-  if (dtype < 0 || op < 0 || type_nbytes == 0) return false;
-  if (comm_.world <= 1 && !cfg.device_force) return false;
-  if (cfg.bootstrap_cache && !checkpoint_loaded_) return false;  // bootstrap ops are keyed by call site, not chunked
-  const size_t per_chunk = std::max<size_t>(cfg.device_host_chunk / type_nbytes, 1);
-  const size_t nchunk = (count + per_chunk - 1) / per_chunk;
-  char *host = static_cast<char *>(buf);
-  char *dev = static_cast<char *>(device_->Alloc(bytes));
-  const int depth = DeviceBackend::kCopySlots - 1;
-  auto begin = [&](size_t i) { return i * per_chunk * type_nbytes; };
-  auto span = [&](size_t i) { return std::min(per_chunk, count - i * per_chunk) * type_nbytes; };
-  for (size_t i = 0; i < nchunk && i < static_cast<size_t>(depth); ++i) {
-    device_->PrefetchH2D(dev + begin(i), host + begin(i), span(i), static_cast<int>(i));
-  }
-  for (size_t i = 0; i < nchunk; ++i) {
-    device_->AwaitPrefetch(static_cast<int>(i));
-    if (i + depth < nchunk) {
-      device_->PrefetchH2D(dev + begin(i + depth), host + begin(i + depth), span(i + depth), static_cast<int>(i + depth));
-    }
-    if (i != 0) BetweenChunks();
-    OpArgs a{};
-    a.kind = OpKind::kAllreduce; a.buf = dev + begin(i); a.bytes = span(i);
-    a.elem_bytes = type_nbytes; a.count = span(i) / type_nbytes; a.reducer = reducer; a.dtype = dtype; a.op = op;
-    a.key = key + "/" + std::to_string(i);
-    RunOp(&a);
-    device_->DrainD2H(host + begin(i), dev + begin(i), span(i));
-  }
-  device_->DrainSync();
-  device_->Free(dev);
+  if (a.kind != OpKind::kAllreduce || device_ == nullptr || !device_->attached()) return false;
+  if (cfg.device_host_min == 0 || a.bytes < cfg.device_host_min) return false;
+  if (a.dtype < 0 || a.op < 0 || a.elem_bytes == 0) return false;
+  if (cfg.bootstrap_cache && !checkpoint_loaded_) return false;  // bootstrap results live in the host cache
   return true;
 }
 
 void RobustEngine::AllreduceTyped(void *buf, size_t type_nbytes, size_t count, ReduceFunction reducer,
                                   int dtype, int op, PreprocFunction prepare_fun, void *prepare_arg,
                                   const char *_file, const int _line, const char *_caller) {
-  if (prepare_fun == nullptr && device_ != nullptr && comm_.cfg.device_host_min != 0 &&
-      Classify(buf) == MemKind::kHost &&
-      HostViaDevice(buf, type_nbytes, count, reducer, dtype, op, std::string(_file) + "::" + std::to_string(_line))) {
-    return;
-  }
   OpArgs a{};
   a.kind = OpKind::kAllreduce; a.buf = buf; a.bytes = type_nbytes * count;
   a.elem_bytes = type_nbytes; a.count = count; a.reducer = reducer; a.dtype = dtype; a.op = op;
   a.prepare_fun = prepare_fun; a.prepare_arg = prepare_arg;
   a.key = std::string(_file) + "::" + std::to_string(_line) + "::" + _caller + "#" +
           std::to_string(type_nbytes) + "x" + std::to_string(count);
+  // An op that goes through the kernels must fit the arena as ONE recoverable unit. What does not (symmetric
+  // buffers pin the arena, or more than 2 GiB) is cut into pieces that are sequence-numbered ops of their own:
+  // each has its own cache entry, commits or fails alone and is replayed alone. Same cut on every rank.
+  const bool kernels = device_ != nullptr && device_->attached() && dtype >= 0 && op >= 0 && type_nbytes != 0 &&
+                       (comm_.world > 1 || comm_.cfg.device_force) &&
+                       !(comm_.cfg.bootstrap_cache && !checkpoint_loaded_) &&
+                       (Classify(buf) == MemKind::kDevice || HostOverDevice(a));
+  if (kernels) {
+    const size_t cap = device_->MaxOpBytes(a.bytes) / type_nbytes * type_nbytes;
+    if (cap != 0 && a.bytes > cap) {
+      bool first = true;
+      for (size_t off = 0; off < a.bytes; off += cap) {
+        OpArgs piece = a;
+        piece.buf = static_cast<char *>(buf) + off;
+        piece.bytes = std::min(cap, a.bytes - off);
+        piece.count = piece.bytes / type_nbytes;
+        piece.key = a.key + "/" + std::to_string(off / cap);
+        if (!first) piece.prepare_fun = nullptr;   // the lazy preparation fills the whole buffer, once
+        RunOp(&piece);
+        first = false;
+      }
+      return;
+    }
+  }
   RunOp(&a);
 }
 

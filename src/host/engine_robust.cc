@@ -76,10 +76,37 @@ bool RobustEngine::Shutdown(void) {
 
 void RobustEngine::InitAfterException(void) {
   // the caller swallowed an engine exception and wants to carry on in this process
-  if (device_) device_->Detach();
-  comm_.CloseLinks();
-  while (!comm_.Connect("recover")) std::this_thread::sleep_for(std::chrono::milliseconds(100));
-  if (device_) device_->Attach(&comm_);
+  this->Rejoin();
+}
+
+/*!
+ * \brief drop every link, meet the others at the tracker's "recover" rendezvous, rebuild the device arena.
+ *  A second peer may die while the survivors are in here (a link breaks during the arena exchange): that is
+ *  one more round of the same loop, not a fatal error.
+ */
+void RobustEngine::Rejoin() {
+  const bool had_device = device_ != nullptr;
+  while (true) {
+    if (device_) device_->Detach();
+    comm_.CloseLinks();
+    std::this_thread::sleep_for(std::chrono::milliseconds(2 * comm_.rank));
+    while (!comm_.Connect("recover")) {
+      utils::Check(!comm_.job_over, "[%d] cannot recover: the other ranks have already shut down", comm_.rank);
+      std::this_thread::sleep_for(std::chrono::milliseconds(100));
+    }
+    if (!had_device && comm_.world <= 1) return;
+    const AttachResult r = this->AttachDevice();
+    if (r == AttachResult::kLinkError) {
+      if (comm_.cfg.debug) {
+        utils::HandleLogInfo("[%d] a link broke while the device arena was being re-attached, re-joining again\n", comm_.rank);
+      }
+      continue;
+    }
+    // cached results and checkpoints of this rank live in the backend's memory: it cannot simply go away
+    utils::Check(!(had_device && r == AttachResult::kNoDevice),
+                 "[%d] device arena could not be re-established after recovery", comm_.rank);
+    return;
+  }
 }
 
 // ------------------------------------------------------------------ failures
@@ -121,16 +148,7 @@ bool RobustEngine::Healthy(Status s) {
   StartWatchdog();
   // Drop EVERY link: neighbours observe it as a failure too and the whole job funnels into the
   // tracker's "recover" rendezvous, where it waits for the replacement process.
-  if (device_) device_->Detach();
-  comm_.CloseLinks();
-  std::this_thread::sleep_for(std::chrono::milliseconds(2 * comm_.rank));
-  while (!comm_.Connect("recover")) {
-    utils::Check(!comm_.job_over, "[%d] cannot recover: the other ranks have already shut down", comm_.rank);
-    std::this_thread::sleep_for(std::chrono::milliseconds(100));
-  }
-  if (device_ && !device_->Attach(&comm_)) {
-    utils::Error("[%d] device arena could not be re-established after recovery", comm_.rank);
-  }
+  this->Rejoin();
   return false;
 }
 
@@ -143,6 +161,8 @@ void EnvelopeReduce(const void *src_, void *dst_, int count, const MPI::Datatype
   proto::Envelope *dst = static_cast<proto::Envelope *>(dst_);
   for (int i = 0; i < count; ++i) {
     dst[i].sum.Merge(src[i].sum);
+    dst[i].dev_epoch = std::max(dst[i].dev_epoch, src[i].dev_epoch);
+    dst[i].dev_rounds = std::max(dst[i].dev_rounds, src[i].dev_rounds);
     const bool same_sig = src[i].signature == dst[i].signature && src[i].bytes == dst[i].bytes;
     const uint32_t a = src[i].state, b = dst[i].state;
     proto::InlineOp *op = tl_inline;
@@ -168,6 +188,8 @@ bool RobustEngine::Consensus(void *buf, size_t size, uint32_t flags, uint32_t se
     me.cache_count = static_cast<uint32_t>(boot_cache_.size());
     std::memset(env.get(), 0, sizeof(proto::Envelope));
     env->sum = Summary::Of(me);
+    const bool dev_up = device_ != nullptr && device_->attached();
+    if (dev_up) { env->dev_epoch = device_->OpEpoch(); env->dev_rounds = device_->OpRounds(); }
     if (inline_op != nullptr) {
       const bool bcast = inline_op->bcast_root >= 0;
       env->state = !bcast ? 1 : (inline_op->bcast_root == comm_.rank ? 4 : 3);
@@ -180,6 +202,7 @@ bool RobustEngine::Consensus(void *buf, size_t size, uint32_t flags, uint32_t se
     const Status st = comm_.AllreduceTree(env.get(), sizeof(proto::Envelope), 1, EnvelopeReduce);
     tl_inline = nullptr;
     if (!Healthy(st)) continue;
+    if (dev_up) device_->AdoptEpoch(env->dev_epoch, env->dev_rounds);
     const Summary sum = env->sum;
     const proto::Verdict v = proto::Decide(sum, me);
     switch (v.action) {

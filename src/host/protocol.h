@@ -92,7 +92,11 @@ struct Envelope {
                        // operation), 3 broadcast receiver, 4 broadcast payload (from the root)
   uint32_t signature;  // identifies the operation: hash of (seq, item size, item count)
   uint32_t bytes;
-  uint32_t reserved;
+  // op counters of the device kernels' flag protocols, folded with max: after a kernel was abandoned on some
+  // ranks (consensus mismatch, failed chunk of a multi-kernel op) the counters differ, and every rank adopts
+  // the largest before the next fused kernel (DeviceBackend::AdoptEpoch)
+  uint32_t dev_epoch;
+  uint64_t dev_rounds;
   unsigned char payload[kInlineBytes];
 };
 /*! \brief reducer context of the rank running the envelope allreduce (thread local, set by Consensus) */

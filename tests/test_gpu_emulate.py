@@ -45,7 +45,7 @@ def _reference(bufs, op):
     return out
 
 
-@pytest.mark.parametrize("algo", [1, 2, 3, 5])
+@pytest.mark.parametrize("algo", [1, 2, 3])
 @pytest.mark.parametrize("n", [2, 8])
 @pytest.mark.parametrize("count", [1, 5, 4096, 100003, 1 << 20])
 def test_allreduce_sum_f32(algo, n, count):
@@ -59,7 +59,7 @@ def test_allreduce_sum_f32(algo, n, count):
 
 @pytest.mark.parametrize("dtype", [torch.int8, torch.uint8, torch.int32, torch.int64, torch.float32, torch.float64])
 @pytest.mark.parametrize("op", [0, 1, 2, 3])
-@pytest.mark.parametrize("algo", [1, 2, 3, 5])
+@pytest.mark.parametrize("algo", [1, 2, 3])
 def test_allreduce_all_types_ops(dtype, op, algo):
     if op == 3 and dtype.is_floating_point:
         pytest.skip("BitOR is undefined on floating point (reference c_api.cc:24-33)")
@@ -72,7 +72,7 @@ def test_allreduce_all_types_ops(dtype, op, algo):
         assert torch.equal(b, want)
 
 
-@pytest.mark.parametrize("algo", [1, 2, 3, 5])
+@pytest.mark.parametrize("algo", [1, 2, 3])
 def test_allreduce_keep_copy_and_unaligned(algo):
     """`keep` (the result-cache copy fused into the epilogue) and a user pointer that is only
     4-byte aligned."""
@@ -106,7 +106,7 @@ def test_pair_sum_histogram_f64():
 def test_repeated_ops_alternate_stages():
     """epoch parity double buffering: many back-to-back ops of different sizes and algorithms"""
     n = 4
-    for i, (count, algo) in enumerate([(1000, 1), (1 << 18, 2), (77, 5), (1 << 18, 3), (4097, 2), (1 << 20, 5), (9, 1)] * 3):
+    for i, (count, algo) in enumerate([(1000, 1), (1 << 18, 2), (77, 2), (1 << 18, 3), (4097, 2), (1 << 20, 1), (9, 1)] * 3):
         bufs = _inputs(n, count, torch.float32, seed=100 + i)
         want = _reference(bufs, 2)
         assert emu.collective(emu.ALLREDUCE, bufs, algo=algo, op=2) == [0] * n
