@@ -4,6 +4,7 @@ two-shot (and TMA) kernel, one cooperative grid per call.  Prints CUDA-event tim
 plain run gives the number and the ncu run only gives the counters.
 
     python benchmarks/profile_emu.py [--algo 2] [--mib 32] [--iters 5]
+    python benchmarks/profile_emu.py --algo 10 --chunk-mib 8     (the streamed allreduce: StreamP2P per chunk)
 """
 import argparse
 import json
@@ -23,17 +24,23 @@ def main():
     ap.add_argument("--ranks", type=int, default=8)
     ap.add_argument("--mib", type=int, default=32)
     ap.add_argument("--iters", type=int, default=5)
+    ap.add_argument("--chunk-mib", type=int, default=8)
     args = ap.parse_args()
     torch.cuda.set_device(0)
     count = args.mib * (1 << 20) // 4
     bufs = [torch.full((count,), float(r + 1), device="cuda") for r in range(args.ranks)]
+    def run():
+        if args.algo == 10:
+            assert emu.stream_allreduce(bufs, op=1, chunk_bytes=args.chunk_mib << 20) == [0] * args.ranks
+        else:
+            emu.collective(emu.ALLREDUCE, bufs, algo=args.algo, op=1)   # Min keeps values bounded
     for _ in range(3):
-        emu.collective(emu.ALLREDUCE, bufs, algo=args.algo, op=1)   # Min keeps values bounded
+        run()
     times = []
     for _ in range(args.iters):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        emu.collective(emu.ALLREDUCE, bufs, algo=args.algo, op=1)
+        run()
         e1.record()
         torch.cuda.synchronize()
         times.append(e0.elapsed_time(e1))

@@ -155,6 +155,21 @@ def broadcast_async_(tensor, root=0):
     return tensor
 
 
+def allgather_async_(out, begin, count):
+    """Enqueue a ring-ordered allgather on the current CUDA stream: this rank owns
+    ``out.view(-1)[begin:begin+count]``, every other range is filled in from its owner."""
+    lib = _lib()
+    _check(out)
+    if not out.is_cuda:
+        raise ValueError("allgather_async_ needs a CUDA tensor")
+    _bind_stream(lib, out)
+    es = out.element_size()
+    rc = lib.RabitDeviceAllgatherAsync(ctypes.c_void_p(out.data_ptr()), out.numel() * es, begin * es, (begin + count) * es)
+    if rc != 0:
+        raise RuntimeError("RabitDeviceAllgatherAsync failed (%d)" % rc)
+    return out
+
+
 def synchronize():
     """Wait for the enqueued collectives; raises if a peer was lost or timed out."""
     rc = _lib().RabitDeviceSynchronize()

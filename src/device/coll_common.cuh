@@ -53,6 +53,10 @@ struct Control {
   // block 0 folds them and posts the grid's verdict in gate_go (no contended atomics)
   unsigned long long gate_slot[kMaxBlocks];
   unsigned long long gate_go;
+  // multi-kernel ops: a kernel that fails leaves (1 << 32 | epoch of the op's FIRST kernel) here; the op's later
+  // kernels look at it before they wait for anybody (device memory on purpose: a read of host memory in front of
+  // the entry barrier makes its system-scope fence cost ~1 us per block, serialised over the grid - measured)
+  unsigned long long op_failed;
 };
 static_assert(sizeof(Control) <= kCtrlBytes, "control block too small");
 
@@ -77,7 +81,8 @@ struct Params {
   unsigned long long timeout_ns;
   unsigned long long *trace;  // optional host-mapped phase timestamps of block 0 (NULL = off)
   int device_epoch;           // 1: take the op epoch from Control::epoch_dev instead of `epoch` (graph-replayable)
-  int chained;                // 1: not the first kernel of a multi-kernel op: leave at once if an earlier one failed
+  int chained;                // index of this kernel inside a multi-kernel op (0 = first, or a single-kernel op):
+                              // a later kernel leaves at once if an earlier one of the same op failed
 };
 
 /*! \brief the op epoch of the running kernel. With device_epoch it was fetched from the control block by BeginOp
@@ -170,10 +175,16 @@ __device__ __forceinline__ int FlagBarrier(const Params &p, int me, RowOf row_of
   return *s_verdict;
 }
 
-/*! \brief record the first failure of this (emulated) rank for the host */
+/*! \brief what a failed kernel of the op that began at epoch `first_epoch` leaves in Control::op_failed */
+__device__ __forceinline__ unsigned long long FailTag(unsigned int first_epoch) {
+  return (1ull << 32) | first_epoch;
+}
+/*! \brief record the first failure of this (emulated) rank for the host, and for the op's later kernels */
 __device__ __forceinline__ void Report(const Params &p, int me, int verdict) {
   if (threadIdx.x == 0 && verdict != kStOk) {
     atomicCAS(p.status + (p.emulate ? me : 0), kStOk, verdict);
+    *reinterpret_cast<volatile unsigned long long *>(&CtrlOf(p, me)->op_failed) =
+        FailTag(OpEpoch(p) - static_cast<unsigned int>(p.chained));
   }
 }
 
@@ -270,11 +281,14 @@ __device__ __forceinline__ void EndOp(const Params &p, int me) {
 
 /*! \brief true when an earlier kernel of the same multi-kernel op already reported a failure (block-uniform).
  *  After a failed chunk the peers may have left for the host protocol (consensus mismatch), so the remaining
- *  kernels of the op must not wait for them. Reads the host-mapped status word: chained kernels only. */
+ *  kernels of the op must not wait for them. */
 __device__ __forceinline__ bool Poisoned(const Params &p, int me) {
   __shared__ int s_poison;
-  if (!p.chained) return false;
-  if (threadIdx.x == 0) s_poison = *reinterpret_cast<volatile int *>(p.status + (p.emulate ? me : 0));
+  if (p.chained == 0) return false;
+  if (threadIdx.x == 0) {
+    const unsigned long long seen = *reinterpret_cast<volatile unsigned long long *>(&CtrlOf(p, me)->op_failed);
+    s_poison = seen == FailTag(OpEpoch(p) - static_cast<unsigned int>(p.chained)) ? 1 : 0;
+  }
   __syncthreads();
   return s_poison != 0;
 }

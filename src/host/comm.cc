@@ -308,6 +308,7 @@ Status HostComm::AllreduceTree(void *buf_, size_t eb, size_t count, ReduceFuncti
   if (scratch_.size() < cap * kids.size()) scratch_.resize(cap * kids.size());
   for (size_t i = 0; i < kids.size(); ++i) kids[i].stage = scratch_.data() + i * cap;
 
+  const size_t fold_min = std::min(std::max(cfg.tree_reduce_minsize / eb * eb, eb), std::max(cap / 2 / eb * eb, eb));
   size_t reduced = kids.empty() ? total : 0;  // prefix of buf that holds the subtree's reduction
   size_t sent_up = 0, recv_down = 0;
   const MPI::Datatype dtype(eb);
@@ -348,6 +349,9 @@ Status HostComm::AllreduceTree(void *buf_, size_t eb, size_t count, ReduceFuncti
       size_t avail = total;
       for (const Child &c : kids) avail = std::min(avail, c.recvd);
       avail = avail / eb * eb;
+      // rabit_tree_reduce_minsize: do not call the reducer (and wake the parent) for every few bytes that
+      // trickle in; wait for a worthwhile piece unless the message ends first (reference allreduce_base.cc:496)
+      if (avail != total && avail - reduced < fold_min) avail = reduced;
       while (reduced < avail) {
         const size_t off = reduced % cap;
         const size_t n = std::min(avail - reduced, cap - off);

@@ -36,7 +36,8 @@ struct Config {
   int slave_port = 0;          // 0 = let the OS pick; >0 = scan [port, port + nport_trial)
   int nport_trial = 1000;
   // ---- host collectives ----
-  size_t tree_reduce_minsize = 1 << 20;      // bytes per pipeline chunk in the tree
+  size_t tree_reduce_minsize = 64 << 10;     // bytes a tree node gathers before it folds and forwards (reference: 1 MiB;
+                                             // smaller here so that the levels of the tree still overlap, doc/parameters.md)
   size_t reduce_ring_mincount = 256 << 10;   // elements; above this the ring is used (reference: 32 Ki; see doc/parameters.md)
   size_t reduce_buffer = 256UL << 20;        // cap of a per-link staging ring
   bool tcp_no_delay = true;                  // reference default is off (Nagle stalls)

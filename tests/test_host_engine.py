@@ -130,3 +130,26 @@ def test_recovery_at_world_31(built):
     assert res.ok, {i: o[-400:] for i, o in res.outputs.items() if "iter 2" not in o}
     assert res.restarts == 4
     assert all("iter 2 checkpointed (version 3)" in o for o in res.outputs.values())
+
+
+@pytest.mark.parametrize("extra", [[], ["rabit_reduce_ring_mincount=10"], ["rabit_reduce_ring_mincount=100000000"],
+                                   ["rabit_reduce_buffer=8", "rabit_reduce_ring_mincount=100000000"]])
+def test_custom_reducers_across_ranks(extra):
+    """Reducer<16-byte struct> (opaque merge, declared packed sum, mixed lanes) and SerializeReducer over
+    tree and ring, world 5; the last case has a per-link buffer smaller than one element"""
+    res = run_job([bin_path("reducer_multi"), "3000"] + extra, 5)
+    assert res.ok, res.outputs
+    assert res.restarts == 0
+
+
+def test_custom_reducers_replayed_after_kill():
+    res = run_job([bin_path("reducer_multi"), "2000", "iters=3", "mock=1,1,1,0", "mock=3,1,3,0"], 4)
+    assert res.ok, res.outputs
+    assert res.restarts == 2
+
+
+def test_tree_reduce_minsize_small_and_large():
+    for v in ("1", "4096", "100000000"):
+        res = run_job([bin_path("model_recover"), "30000", "rabit_reduce_ring_mincount=100000000",
+                       "rabit_tree_reduce_minsize=" + v], 6)
+        assert res.ok, res.outputs
