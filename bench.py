@@ -216,7 +216,7 @@ def run_ours(args):
     big_bytes = max(S, 1 << 30) if not args.no_sweep else S
     init_args = ["rabit_device=on", "rabit_device_algo=" + args.algo,
                  "rabit_device_arena=%d" % (2 * (big_bytes + 4096) + (1 << 20)),
-                 "rabit_device_heap=%d" % (S + big_bytes + (8 << 20)),
+                 "rabit_device_heap=%d" % (S + big_bytes + (768 << 20)),
                  "rabit_device_cache=64G"]
     init_args += [a for a in args.extra.split(",") if a]
     if world > 1:

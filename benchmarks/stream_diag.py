@@ -1,7 +1,14 @@
 #!/usr/bin/env python
-"""Where does the time of a streamed allreduce go?  One GPU (rabit_device_force), or one rank per GPU under the
-launcher.  For a few chunk plans: device time per 256 MiB op on the async and the blocking API, and block 0's
-phase stamps of the LAST chunk kernel (us: entry barrier, reduce, mid barrier, epilogue / gather)."""
+"""Chunk-plan sweep of the streamed allreduce (where does the time go, which plan wins at this world size?).
+
+    python benchmarks/stream_diag.py                                              one GPU (kernels forced on)
+    python -m rabit_b200.parallel.launcher -n 8 --gpus python benchmarks/stream_diag.py [plans=8M:64M,32M:512M] [mib=256]
+
+For every plan "first:chunk" (and for the single-launch kernels, "legacy"): device time per op on the async API
+and on the blocking fault-tolerant API, on an ordinary tensor and on a symmetric one, max over ranks; block 0's
+phase stamps of the LAST chunk kernel (us: entry barrier, reduce, mid barrier, epilogue / gather).
+One JSON line per plan on rank 0.
+"""
 import json
 import os
 import sys
@@ -14,21 +21,29 @@ from rabit_b200 import rabit, torch_binding as rt  # noqa: E402
 
 
 def main():
-    S = 256 << 20
-    plans = [("8M", "64M"), ("256M", "256M"), ("16M", "32M")]
+    mib = 256
+    plans = [("8M", "64M"), ("32M", "512M"), ("512M", "512M")]
+    for a in sys.argv[1:]:
+        if a.startswith("plans="):
+            plans = [tuple(p.split(":")) for p in a[6:].split(",")]
+        if a.startswith("mib="):
+            mib = int(a[4:])
+    S = mib << 20
     ordinal = int(os.environ.get("RABIT_DEVICE_ORDINAL", os.environ.get("RABIT_LOCAL_RANK", "0")))
     torch.cuda.set_device(ordinal % torch.cuda.device_count())
-    out = []
+    passthrough = [a for a in sys.argv if a.startswith("rabit_") or a.startswith("DMLC_")]
     for first, chunk in plans + [("legacy", "legacy")]:
-        args = list(sys.argv) + ["rabit_device=on", "rabit_device_arena=%d" % (2 * S + (4 << 20)), "rabit_device_force=1",
-                                 "rabit_device_cache=32G"]
+        args = passthrough + ["rabit_device=on", "rabit_device_arena=%d" % (2 * S + (4 << 20)), "rabit_device_force=1",
+                              "rabit_device_cache=32G", "rabit_device_heap=%d" % (S + (4 << 20))]
         if first == "legacy":
             args += ["rabit_device_algo=nostream"]
         else:
-            args += ["rabit_device_stream_first=" + first, "rabit_device_stream_chunk=" + chunk]
+            args += ["rabit_device_stream_first=" + first, "rabit_device_stream_chunk=" + chunk, "rabit_device_stream_min=1M"]
+        args += [a for a in sys.argv[1:] if a.startswith("rabit_device_host_chunk=")]
         rabit.init(args)
-        me = rabit.get_rank()
+        me, n = rabit.get_rank(), rabit.get_world_size()
         x = torch.ones(S // 4, device="cuda")
+        xs = rt.symmetric_empty(S // 4, torch.float32) if n > 1 else x
         rt.set_tuning(trace=True)
 
         def timed(fn, sync, steps=10, warm=3):
@@ -44,19 +59,39 @@ def main():
             sync()
             torch.cuda.synchronize()
             return float(rabit.allreduce(np.array([e0.elapsed_time(e1) / steps]), rabit.MAX)[0])
-        row = {"first": first, "chunk": chunk}
-        row["async_ms"] = timed(lambda: rt.allreduce_async_(x), rt.synchronize)
+        row = {"world": n, "mib": mib, "first": first, "chunk": chunk}
+        row["async_plain_ms"] = timed(lambda: rt.allreduce_async_(x), rt.synchronize)
         tr = rt.get_trace()
         row["last_kernel_phases_us"] = [round((tr[i] - tr[j]) / 1e3, 1) for i, j in ((2, 0), (3, 2), (4, 3), (5, 4))]
-        for _ in range(14):
-            rabit.allreduce(x, rabit.SUM)
+        for t, key in ((x, "robust_plain_ms"), (xs, "robust_sym_ms")):
+            if key == "robust_sym_ms" and n == 1:
+                continue
+            for _ in range(14):
+                rabit.allreduce(t, rabit.SUM)
+            rabit.checkpoint(0)
+            t.fill_(1.0)
+            row[key] = timed(lambda: rabit.allreduce(t, rabit.SUM), torch.cuda.synchronize)
+            if key == "robust_plain_ms":
+                tr = rt.get_trace()
+                row["robust_last_kernel_phases_us"] = [round((tr[i] - tr[j]) / 1e3, 1) for i, j in ((2, 0), (3, 2), (4, 3), (5, 4))]
+            rabit.checkpoint(0)
+        if n > 1:
+            row["async_sym_ms"] = timed(lambda: rt.allreduce_async_(xs), rt.synchronize)
+        # pinned host tensor through the same call (H2D | kernels | D2H), wall clock
+        import time
+        h = torch.ones(S // 4).pin_memory()
+        for _ in range(6):
+            rt.allreduce_(h)
         rabit.checkpoint(0)
-        x.fill_(1.0)
-        row["robust_ms"] = timed(lambda: rabit.allreduce(x, rabit.SUM), torch.cuda.synchronize)
+        h.fill_(1e-6)
+        rabit.allreduce(np.zeros(1, dtype=np.float32), rabit.SUM)
+        t0 = time.perf_counter()
+        for _ in range(5):
+            rt.allreduce_(h)
+        row["host_tensor_ms"] = float(rabit.allreduce(np.array([(time.perf_counter() - t0) * 1e3 / 5]), rabit.MAX)[0])
         rabit.checkpoint(0)
         if me == 0:
-            out.append(row)
-            print(json.dumps(row), flush=True)
+            print("DIAG " + json.dumps(row), flush=True)
         rabit.finalize()
 
 

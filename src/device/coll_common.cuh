@@ -57,6 +57,12 @@ struct Control {
   // kernels look at it before they wait for anybody (device memory on purpose: a read of host memory in front of
   // the entry barrier makes its system-scope fence cost ~1 us per block, serialised over the grid - measured)
   unsigned long long op_failed;
+  // peer-copy transport (coll_blob.cuh): piece counters written by the other end of a transfer.
+  // deliver: one holder -> requesters; shift[d]: ring neighbours, d = 0 forward (from the predecessor), 1 backward
+  unsigned long long blob_ready[kMaxRanks];   // [holder]: "piece k is in my window"
+  unsigned long long blob_done[kMaxRanks];    // [requester]: "I have taken piece k"
+  unsigned long long shift_ready[2];
+  unsigned long long shift_done[2];
 };
 static_assert(sizeof(Control) <= kCtrlBytes, "control block too small");
 

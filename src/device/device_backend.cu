@@ -33,6 +33,7 @@
 #include "coll_nvls.cuh"
 #include "coll_inplace.cuh"
 #include "coll_stream.cuh"
+#include "coll_blob.cuh"
 #include "coll_ll.cuh"
 #include "device_backend.h"
 #include "../host/engine_core.h"

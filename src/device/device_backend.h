@@ -13,6 +13,7 @@
 #include <cstddef>
 #include <cstdint>
 #include <string>
+#include <vector>
 
 #include "../host/comm.h"
 
@@ -26,6 +27,7 @@ struct DeviceStats {
   uint64_t fused_consensus_mismatch = 0;
   uint64_t timeouts = 0;
   uint64_t streamed_ops = 0;      // allreduces that ran as chunked, copy-engine fed ops
+  uint64_t blob_bytes = 0;        // recovery / replica payload bytes this rank offered over NVLink
   int nvls = 0;                   // multicast path usable
   int p2p = 0;                    // peer mappings established
 };
@@ -81,6 +83,19 @@ class DeviceBackend {
   virtual Status Broadcast(void *dptr, size_t size, int root, uint32_t code, void *keep, int flags = 0) = 0;
   virtual Status Allgather(void *dptr, size_t total, size_t slice_begin, size_t slice_end,
                            uint32_t code, void *keep) = 0;
+
+  // ---- recovery payloads over NVLink: copy engines on a side stream, only the two ends take part ----
+  /*!
+   * \brief move `size` bytes from rank `holder` (src_dev if not NULL, else src_host) to every rank r with need[r]
+   *  (landing in dst_host there). ALL ranks call it with the same holder / need / size; the others return at once.
+   */
+  virtual Status BlobDeliver(int holder, const std::vector<char> &need, const void *src_host, const void *src_dev,
+                             void *dst_host, size_t size) = 0;
+  /*!
+   * \brief ring neighbour exchange of host blobs: offer `out` to the successor (forward) or predecessor and take
+   *  `in_len` bytes from the other neighbour. Both ends of each transfer must call it (a length of 0 = nothing).
+   */
+  virtual Status BlobShift(const void *out, size_t out_len, void *in, size_t in_len, bool forward) = 0;
 
   // ---- plain memory services for the engines (staging, result cache) ----
   virtual void *Alloc(size_t nbytes) = 0;

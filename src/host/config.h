@@ -71,6 +71,7 @@ struct Config {
   std::string device_algo = "auto";          // auto|oneshot|twoshot|tma|nvls
   bool device_force = false;                 // run kernels even at world size 1
   size_t device_cache_bytes = 16UL << 30;    // device-resident result cache budget
+  size_t device_blob_min = 32UL << 10;       // bytes: recovery payloads / checkpoint replicas >= this move by NVLink peer copies
   size_t device_host_min = 4UL << 20;        // bytes: HOST buffers >= this ride PCIe + NVLink instead of TCP; 0 = off
   size_t device_host_chunk = 32UL << 20;     // pipeline granule of that path (H2D | kernel | D2H overlap)
 
@@ -86,7 +87,7 @@ struct Config {
       "rabit_device_blocks", "rabit_device_timeout_ms", "rabit_device_force",
       "rabit_device_oneshot_max", "rabit_device_nvls_min", "rabit_device_ll_max", "rabit_device_heap", "rabit_device_cache",
       "rabit_device_stream_min", "rabit_device_stream_chunk", "rabit_device_stream_first", "rabit_device_tune",
-      "rabit_device_host_min", "rabit_device_host_chunk",
+      "rabit_device_host_min", "rabit_device_host_chunk", "rabit_device_blob_min",
       "rabit_world_size", "rabit_slave_port"};
     return names;
   }
@@ -156,6 +157,7 @@ struct Config {
     else if (is("rabit_device_nvls_min")) device_nvls_min = ParseBytes(name, val);
     else if (is("rabit_device_cache")) device_cache_bytes = ParseBytes(name, val);
     else if (is("rabit_device_host_min")) device_host_min = ParseBytes(name, val);
+    else if (is("rabit_device_blob_min")) device_blob_min = ParseBytes(name, val);
     else if (is("rabit_device_host_chunk")) device_host_chunk = std::max<size_t>(ParseBytes(name, val), 64UL << 10);
     else if (is("rabit_device_blocks")) device_blocks = atoi(val);
     else if (is("rabit_device_timeout_ms")) device_timeout_ms = atoi(val);

@@ -58,7 +58,12 @@ bool BaseEngine::Init(int argc, char *argv[]) {
                  comm_.cfg.tracker_port);
   }
   if (comm_.world > 1 || comm_.cfg.device_force) {
+    const double t_dev = utils::GetTime();
     device_.reset(DeviceBackend::Create(comm_.cfg));
+    if (getenv("RABIT_RECOVER_PROFILE") != nullptr) {
+      utils::HandleLogInfo("[%d] init: CUDA context + backend set-up %.1f ms (attempt %d)\n", comm_.rank,
+                           (utils::GetTime() - t_dev) * 1e3, comm_.cfg.num_trial);
+    }
     // (a link that breaks this early is fatal here; the robust engine re-joins instead, see RobustEngine::Init)
     utils::Check(this->AttachDevice() != AttachResult::kLinkError, "lost a peer while setting up the device arena");
   }

@@ -231,6 +231,8 @@ class RobustEngine : public BaseEngine {
   void (*on_timeout)(int rank, int seconds) = nullptr;
   /*! \brief number of link failures handled so far */
   int recover_count() const { return recover_counter_; }
+  uint64_t nvlink_payload_bytes() const { return nvlink_payload_bytes_; }
+  uint64_t tcp_payload_bytes() const { return tcp_payload_bytes_; }
   /*! \brief feed a primitive's status through the failure handler (tests) */
   bool HandleStatus(Status s) { return this->Healthy(s); }
   /*! \brief true while a watchdog thread is counting down */
@@ -276,9 +278,9 @@ class RobustEngine : public BaseEngine {
   /*! \brief gather `nwords` 64-bit words from every rank into a world x nwords table */
   Status GatherTable(const uint64_t *mine, int nwords, std::vector<uint64_t> *table);
   /*!
-   * \brief large recovery payloads go over NVLink instead of the TCP ring when every rank has a device
-   *  backend: the lowest-ranked holder uploads the blob, ONE broadcast kernel (multicast store where the
-   *  switch supports it) fans it out, requesters download it. Returns false if that path is not usable.
+   * \brief recovery payloads go over NVLink instead of the TCP ring when the device arena is up: the lowest-ranked
+   *  holder puts the blob into its arena window, the requesters' copy engines pull it from there on a side
+   *  stream; nobody else takes part. Returns false if that path is not usable (then the ring delivers).
    */
   bool DeviceDeliver(const std::vector<char> &has, const std::vector<char> &need, const void *src_host,
                      const void *src_dev, void *dst_host, size_t size, Status *st);
@@ -313,6 +315,8 @@ class RobustEngine : public BaseEngine {
   int num_local_replica_ = 0;
   int use_local_model_ = -1;
   int recover_counter_ = 0;
+  // bytes of recovery payloads / checkpoint replicas this rank sent or received, by transport (rabit_debug log)
+  uint64_t nvlink_payload_bytes_ = 0, tcp_payload_bytes_ = 0;
   std::thread watchdog_;
   std::atomic<bool> watchdog_cancel_{false};
   std::atomic<bool> watchdog_done_{true};

@@ -59,6 +59,7 @@ Status RobustEngine::ServeResult(void *buf, size_t size, uint32_t seq, bool requ
   if (held != nullptr && !has[(comm_.rank + 1) % n]) p = results_.HostView(held);
   if (held != nullptr && p == nullptr) return Status::kOk;
   dst = RingDeliver(has, need, p, held_size);
+  tcp_payload_bytes_ += p != nullptr ? held_size : 0;
   if (Ok(dst) && requester && held_size != 0) std::memcpy(buf, landing.data(), held_size);
   return dst;
 }
@@ -66,23 +67,21 @@ Status RobustEngine::ServeResult(void *buf, size_t size, uint32_t seq, bool requ
 bool RobustEngine::DeviceDeliver(const std::vector<char> &has, const std::vector<char> &need,
                                  const void *src_host, const void *src_dev, void *dst_host, size_t size,
                                  Status *st) {
-  const size_t kMinBytes = 4u << 20;  // below this the TCP ring is as fast and needs no GPU round trip
-  if (device_ == nullptr || !device_->attached() || size < kMinBytes) return false;
-  int root = -1;
-  for (int r = 0; r < comm_.world && root < 0; ++r) if (has[r]) root = r;
-  if (root < 0) return false;
-  // every rank takes part in the kernel, whether it needs the bytes or not
-  void *d = device_->Alloc(size);
-  if (comm_.rank == root) {
-    if (src_dev != nullptr) device_->CopyD2D(d, src_dev, size);
-    else device_->CopyH2D(d, src_host, size);
-  }
-  *st = device_->Broadcast(d, size, root, 0x7ffffff0u, nullptr);
-  if (Ok(*st) && need[comm_.rank] && dst_host != nullptr) device_->CopyD2H(dst_host, d, size);
-  device_->Free(d);
-  if (comm_.cfg.debug) {
-    utils::HandleLogInfo("[%d] recovery payload of %lu bytes moved over NVLink from rank %d (%s)\n", comm_.rank,
-                         static_cast<unsigned long>(size), root, StatusName(*st));  // NOLINT(*)
+  // below rabit_device_blob_min the TCP ring is as fast and needs no GPU round trip
+  if (device_ == nullptr || !device_->attached() || size < comm_.cfg.device_blob_min || size == 0) return false;
+  int holder = -1;
+  for (int r = 0; r < comm_.world && holder < 0; ++r) if (has[r]) holder = r;
+  if (holder < 0) return false;
+  // ONE holder serves: its copy engine puts the bytes into its arena window, every requester pulls them over
+  // NVLink through its mapping of that arena. Ranks that neither hold nor need the bytes only keep count.
+  const double t0 = utils::GetTime();
+  *st = device_->BlobDeliver(holder, need, src_host, src_dev, dst_host, size);
+  nvlink_payload_bytes_ += (comm_.rank == holder || need[comm_.rank]) ? size : 0;
+  if (comm_.cfg.debug && (comm_.rank == holder || need[comm_.rank])) {
+    const double dt = utils::GetTime() - t0;
+    utils::HandleLogInfo("[%d] recovery payload of %lu bytes moved over NVLink from rank %d (%s, %.3f ms, %.1f GB/s)\n",
+                         comm_.rank, static_cast<unsigned long>(size), holder, StatusName(*st), dt * 1e3,  // NOLINT(*)
+                         dt > 0 ? size / dt / 1e9 : 0.0);
   }
   return true;
 }
@@ -138,6 +137,7 @@ Status RobustEngine::ServeLoad(bool requester) {
                      size, &dst)) {
     void *p = requester ? static_cast<void *>(&incoming[0]) : (holder ? static_cast<void *>(&global_blob_[0]) : nullptr);
     dst = RingDeliver(has, need, p, size);
+    tcp_payload_bytes_ += p != nullptr ? size : 0;
   }
   if (Ok(dst) && requester) global_blob_.swap(incoming);
   return dst;
@@ -197,7 +197,10 @@ Status RobustEngine::ServeCache(bool requester, uint32_t max_count) {
   }
   utils::Check(any && size != 0, "[%d] bootstrap cache: nobody holds %u entries", comm_.rank, max_count);
   if (requester) blob.resize(size);
-  st = RingDeliver(has, need, (requester || holder) ? &blob[0] : nullptr, size);
+  if (!DeviceDeliver(has, need, holder ? blob.data() : nullptr, nullptr, requester ? &blob[0] : nullptr, size, &st)) {
+    st = RingDeliver(has, need, (requester || holder) ? &blob[0] : nullptr, size);
+    tcp_payload_bytes_ += (requester || holder) ? size : 0;
+  }
   if (!Ok(st)) return st;
   if (requester) BootDeserialize(blob);
   return Status::kOk;
@@ -229,8 +232,21 @@ Status RobustEngine::CompleteLocal(int g) {
     Status s = comm_.RingShift(&out_len, send ? sizeof(out_len) : 0, &in_len, recv ? sizeof(in_len) : 0, forward);
     if (!Ok(s)) return s;
     if (recv) slot[dj].resize(in_len);
-    s = comm_.RingShift(send ? slot[sj].data() : nullptr, out_len, recv ? &slot[dj][0] : nullptr, in_len, forward);
+    // the blobs themselves go neighbour to neighbour over NVLink (copy engines on the side stream) when the arena
+    // is up; each end decides from the length of ITS transfer, which both ends of that transfer know
+    const bool dev_up = device_ != nullptr && device_->attached();
+    const size_t blob_min = std::max<size_t>(comm_.cfg.device_blob_min, 1);
+    const bool out_dev = dev_up && out_len >= blob_min, in_dev = dev_up && in_len >= blob_min;
+    if (out_dev || in_dev) {
+      s = device_->BlobShift(out_dev ? slot[sj].data() : nullptr, out_dev ? out_len : 0,
+                             in_dev ? &slot[dj][0] : nullptr, in_dev ? in_len : 0, forward);
+      if (!Ok(s)) return s;
+      nvlink_payload_bytes_ += (out_dev ? out_len : 0) + (in_dev ? in_len : 0);
+    }
+    const size_t tcp_out = out_dev ? 0 : out_len, tcp_in = in_dev ? 0 : in_len;
+    s = comm_.RingShift(tcp_out != 0 ? slot[sj].data() : nullptr, tcp_out, tcp_in != 0 ? &slot[dj][0] : nullptr, tcp_in, forward);
     if (!Ok(s)) return s;
+    tcp_payload_bytes_ += tcp_out + tcp_in;
     if (recv) mine[dj] = 1;
     // replay the step for the whole table so that all ranks keep the same picture
     std::vector<int> gained;
@@ -258,6 +274,11 @@ Status RobustEngine::CompleteLocal(int g) {
   }
   utils::Check(all_full || all_empty,
                "LoadCheckPoint: too many nodes fails, cannot recover local state");
+  if (comm_.cfg.debug) {
+    utils::HandleLogInfo("[%d] local state complete (generation %d): payload bytes so far over NVLink %lu, over TCP %lu\n",
+                         comm_.rank, g, static_cast<unsigned long>(nvlink_payload_bytes_),  // NOLINT(*)
+                         static_cast<unsigned long>(tcp_payload_bytes_));                   // NOLINT(*)
+  }
   return Status::kOk;
 }
 

@@ -12,6 +12,7 @@
  *     meaningless, and on TCP the ring links already exist.
  */
 #include <chrono>
+#include <cstdlib>
 #include <thread>
 
 #include "../device/device_backend.h"
@@ -86,14 +87,18 @@ void RobustEngine::InitAfterException(void) {
  */
 void RobustEngine::Rejoin() {
   const bool had_device = device_ != nullptr;
+  static const bool profile = getenv("RABIT_RECOVER_PROFILE") != nullptr;
+  const double t0 = utils::GetTime();
   while (true) {
     if (device_) device_->Detach();
     comm_.CloseLinks();
+    const double t1 = utils::GetTime();
     std::this_thread::sleep_for(std::chrono::milliseconds(2 * comm_.rank));
     while (!comm_.Connect("recover")) {
       utils::Check(!comm_.job_over, "[%d] cannot recover: the other ranks have already shut down", comm_.rank);
       std::this_thread::sleep_for(std::chrono::milliseconds(100));
     }
+    const double t2 = utils::GetTime();
     if (!had_device && comm_.world <= 1) return;
     const AttachResult r = this->AttachDevice();
     if (r == AttachResult::kLinkError) {
@@ -105,6 +110,11 @@ void RobustEngine::Rejoin() {
     // cached results and checkpoints of this rank live in the backend's memory: it cannot simply go away
     utils::Check(!(had_device && r == AttachResult::kNoDevice),
                  "[%d] device arena could not be re-established after recovery", comm_.rank);
+    if (profile || comm_.cfg.debug) {
+      utils::HandleLogInfo("[%d] re-join: detach+close %.1f ms, rendezvous (incl. waiting for the replacement) %.1f ms, "
+                           "device attach %.1f ms\n", comm_.rank, (t1 - t0) * 1e3, (t2 - t1) * 1e3,
+                           (utils::GetTime() - t2) * 1e3);
+    }
     return;
   }
 }

@@ -58,12 +58,16 @@ int main(int argc, char *argv[]) {
     }
     {
       std::vector<Mixed> mx(n);
-      for (size_t i = 0; i < n; ++i) { mx[i].lo = static_cast<float>((i * 7 + me * 3) % 11); mx[i].hits = me + 1; mx[i].total = i + 0.25 * me; }
+      for (size_t i = 0; i < n; ++i) {
+        mx[i].lo = static_cast<float>((i * 7 + me * 3) % 11); mx[i].hits = me + 1; mx[i].total = i + 0.25 * me;
+      }
       rabit::Reducer<Mixed, MixedMerge> red;
       red.Allreduce(mx.data(), n);
       for (size_t i = 0; i < n; ++i) {
         float lo = 1e30f; int hits = 0; double total = 0;
-        for (int r = 0; r < world; ++r) { lo = std::min(lo, static_cast<float>((i * 7 + r * 3) % 11)); hits += r + 1; total += i + 0.25 * r; }
+        for (int r = 0; r < world; ++r) {
+          lo = std::min(lo, static_cast<float>((i * 7 + r * 3) % 11)); hits += r + 1; total += i + 0.25 * r;
+        }
         rabit::utils::Check(mx[i].lo == lo && mx[i].hits == hits && mx[i].total == total,
                             "[%d] mixed-lane reducer mismatch at %lu (iter %d)", me, static_cast<unsigned long>(i), it);  // NOLINT(*)
       }
@@ -71,12 +75,16 @@ int main(int argc, char *argv[]) {
     {
       const size_t nobj = 5;
       std::vector<Bag> bags(nobj);
-      for (size_t j = 0; j < nobj; ++j) for (int k = 0; k <= me % 3; ++k) bags[j].items.push_back(static_cast<int>(j * 100 + me * 4 + k));
+      for (size_t j = 0; j < nobj; ++j) {
+        for (int k = 0; k <= me % 3; ++k) bags[j].items.push_back(static_cast<int>(j * 100 + me * 4 + k));
+      }
       rabit::SerializeReducer<Bag> sred;
       sred.Allreduce(bags.data(), 8 + 4 * 3 * static_cast<size_t>(world) + 16, nobj);
       for (size_t j = 0; j < nobj; ++j) {
         std::vector<int> want;
-        for (int r = 0; r < world; ++r) for (int k = 0; k <= r % 3; ++k) want.push_back(static_cast<int>(j * 100 + r * 4 + k));
+        for (int r = 0; r < world; ++r) {
+          for (int k = 0; k <= r % 3; ++k) want.push_back(static_cast<int>(j * 100 + r * 4 + k));
+        }
         std::sort(want.begin(), want.end());
         rabit::utils::Check(bags[j].items == want, "[%d] serialize reducer mismatch in object %lu (iter %d)", me,
                             static_cast<unsigned long>(j), it);  // NOLINT(*)

@@ -101,7 +101,7 @@ def main():
             rabit.allreduce(sx, rabit.MAX)
             want = torch.stack([contribution(sx.numel(), r, it, 103, dev) for r in range(world)]).max(0).values
             assert torch.equal(sx, want), "[%d] symmetric max mismatch iter %d" % (me, it)
-            if not any(a.startswith("mock=") for a in sys.argv):
+            if not any(a.startswith("mock=") for a in sys.argv) and "RABIT_TEST_STREAM_KILL" not in os.environ:
                 # the async API reduces heap buffers in place (zero-copy kernels); it is not sequence-numbered,
                 # so it cannot be part of a run that replays iterations after a kill
                 sx.copy_(contribution(sx.numel(), me, it, 107, dev))
@@ -115,6 +115,43 @@ def main():
                 sb.zero_()
             rt.broadcast_(sb, root)
             assert torch.equal(sb, btruth[:sb.numel()]), "[%d] symmetric broadcast mismatch iter %d" % (me, it)
+        if any(a == "stream=1" for a in sys.argv):
+            # the chunked (streamed) allreduce on an ordinary tensor, on a symmetric tensor and on a host tensor:
+            # small rabit_device_stream_* values make a few MiB run as several chunk kernels
+            sn = 3 * (1 << 20) + 1000
+            t = contribution(sn, me, it, 127, dev)
+            rabit.allreduce(t, rabit.SUM)
+            want = torch.stack([contribution(sn, r, it, 127, dev) for r in range(world)]).sum(0)
+            assert torch.equal(t, want), "[%d] streamed allreduce mismatch iter %d" % (me, it)
+            t = contribution(sn, me, it, 131, dev)
+            rabit.allreduce(t, rabit.MAX)
+            want = torch.stack([contribution(sn, r, it, 131, dev) for r in range(world)]).max(0).values
+            assert torch.equal(t, want), "[%d] streamed max mismatch iter %d" % (me, it)
+            td = contribution(sn // 2, me, it, 59, dev).double()
+            rabit.allreduce(td, rabit.SUM)
+            want = torch.stack([contribution(sn // 2, r, it, 59, dev).double() for r in range(world)]).sum(0)
+            assert torch.equal(td, want), "[%d] streamed f64 mismatch iter %d" % (me, it)
+            if sym is not None:
+                sx = sym[0]
+                sx.copy_(contribution(sx.numel(), me, it, 137, dev))
+                rabit.allreduce(sx, rabit.SUM)
+                want = torch.stack([contribution(sx.numel(), r, it, 137, dev) for r in range(world)]).sum(0)
+                assert torch.equal(sx, want), "[%d] streamed symmetric allreduce mismatch iter %d" % (me, it)
+            th = contribution(sn, me, it, 139, dev).cpu().pin_memory()
+            rt.allreduce_(th, rabit.SUM)
+            want = torch.stack([contribution(sn, r, it, 139, dev) for r in range(world)]).sum(0).cpu()
+            assert torch.equal(th, want), "[%d] streamed host allreduce mismatch iter %d" % (me, it)
+            # async flavour of the same path (no undo, no cache; not sequence-numbered, so not in runs with kills)
+            if any(a.startswith("mock=") for a in sys.argv) or "RABIT_TEST_STREAM_KILL" in os.environ:
+                continue_async = False
+            else:
+                continue_async = True
+            t = contribution(sn, me, it, 149, dev)
+            if continue_async:
+                rt.allreduce_async_(t)
+                rt.synchronize()
+                want = torch.stack([contribution(sn, r, it, 149, dev) for r in range(world)]).sum(0)
+                assert torch.equal(t, want), "[%d] streamed async allreduce mismatch iter %d" % (me, it)
         if any(a == "hostpipe=1" for a in sys.argv):
             # large HOST buffers ride PCIe + NVLink in chunks (rabit_device_host_min): pageable numpy and pinned torch
             hn = 3 * (1 << 20) + 17
