@@ -174,19 +174,20 @@ def max_over_ranks(rabit, np, value):
     return float(rabit.allreduce(np.array([value], dtype=np.float64), rabit.MAX)[0])
 
 
-def recovery_seconds(exe_args, world, per_rank_gpu, repeat=1, timeout=600):
+def recovery_seconds(exe_args, world, per_rank_gpu, repeat=1, timeout=600, standby=False):
     """(wall(run with 2 scripted kills) - wall(same run, no kills)) / 2 under OUR launcher (SURVEY section 6;
     scenario test/test.mk:15-16 of the reference). Returns a dict, or {"error": ...}."""
     from rabit_b200.parallel.launcher import launch
     common = ["rabit_bootstrap_cache=1", "rabit_enable_tcp_no_delay=true"]
     kills = [k for k in ("mock=0,0,1,0", "mock=1,1,1,0") if int(k.split("=")[1].split(",")[0]) < world]
-    out = {"world": world, "scenario": "model_recover, kills " + " ".join(kills)}
+    out = {"world": world, "scenario": "model_recover, kills " + " ".join(kills), "standby_workers": standby}
     try:
         walls = {}
         for name, extra in (("no_kill", []), ("kills", kills)):
             best = None
             for _ in range(repeat):
-                res = launch(exe_args + common + extra, world, capture=True, timeout=timeout, per_rank_gpu=per_rank_gpu)
+                res = launch(exe_args + common + extra, world, capture=True, timeout=timeout, per_rank_gpu=per_rank_gpu,
+                             standby=standby)
                 if not res.ok:
                     return {"error": "job failed (%s): %s" % (name, str(res.returncodes)[:200])}
                 best = res.wall if best is None else min(best, res.wall)
@@ -474,7 +475,11 @@ def run_ours(args):
                 store.get("bench_done_%d" % q)
             exe = os.path.join(ROOT, "build", "bin", "device_recover_cuda")
             if os.path.isfile(exe):
-                recovery = recovery_seconds([exe, "200000"], n, per_rank_gpu=True)
+                # the launcher's standby workers (a pre-started process per task, CUDA context ready) are part of
+                # this framework; the same scenario without them is reported next to it
+                recovery = recovery_seconds([exe, "200000"], n, per_rank_gpu=True, standby=True)
+                cold = recovery_seconds([exe, "200000"], n, per_rank_gpu=True, standby=False)
+                recovery["without_standby_workers"] = cold
             else:
                 recovery = {"error": "build/bin/device_recover_cuda missing"}
             store.set("bench_recovery_done", "1")

@@ -23,6 +23,7 @@ import os
 import shlex
 import subprocess
 import sys
+import tempfile
 import threading
 import time
 
@@ -79,12 +80,18 @@ def ssh_command(ssh, host, cwd, env, cmd):
 
 
 def launch(cmd, nworker, max_attempts=20, env=None, capture=False, timeout=None,
-           per_rank_gpu=False, verbose=False, host="127.0.0.1", hosts=None, ssh=("ssh", "-o", "StrictHostKeyChecking=no")):
+           per_rank_gpu=False, verbose=False, host="127.0.0.1", hosts=None, ssh=("ssh", "-o", "StrictHostKeyChecking=no"),
+           standby=False):
     """Run ``cmd`` (argv list) as ``nworker`` processes under a fresh tracker.
 
     per_rank_gpu: export RABIT_DEVICE_ORDINAL / RABIT_LOCAL_RANK so a task uses the GPU with its index on its host.
     hosts: None = all workers on this machine; otherwise [(host, slots)] and the workers are started through ``ssh``
       (``host`` is then the address under which the remote workers reach the tracker).
+    standby: keep one pre-started process per task (local workers only): it runs the program up to ``rabit::Init``,
+      where the engine creates the CUDA context and then sleeps on a fifo (``RABIT_STANDBY_FIFO``). When the live
+      worker of the task dies, the standby is handed its life (one line with the attempt number) instead of a new
+      process being started, and a fresh standby is started behind it. Recover-after-kill then no longer contains
+      process start-up, library loading and CUDA context creation.
     """
     placement = place_tasks(hosts, nworker) if hosts else None
     tracker = Tracker(nworker, host=host, verbose=verbose).start()
@@ -93,30 +100,77 @@ def launch(cmd, nworker, max_attempts=20, env=None, capture=False, timeout=None,
     deadline = None if timeout is None else time.time() + timeout
     procs = {}
 
+    use_standby = standby and placement is None
+    fifo_dir = tempfile.mkdtemp(prefix="rabit-standby-") if use_standby else None
+    fifo_count = [0]
+
+    def start(i, attempt, fifo=None):
+        wenv = dict(os.environ)
+        if env:
+            wenv.update(env)
+        wenv.update(tracker.worker_env())
+        wenv["DMLC_TASK_ID"] = str(i)
+        wenv["DMLC_NUM_ATTEMPT"] = str(attempt)
+        local = i if placement is None else placement[i][1]
+        wenv["RABIT_LOCAL_RANK"] = str(local)
+        if per_rank_gpu:
+            wenv["RABIT_DEVICE_ORDINAL"] = str(local)
+        if fifo is not None:
+            wenv["RABIT_STANDBY_FIFO"] = fifo
+        kw = {}
+        if capture:
+            kw = dict(stdout=subprocess.PIPE, stderr=subprocess.STDOUT)
+        argv = cmd
+        if placement is not None:
+            # only what the job needs travels: the launcher's own environment stays here
+            keep = dict((k, v) for k, v in wenv.items()
+                        if k.startswith(("DMLC_", "RABIT_", "rabit_")) or (env and k in env))
+            argv = ssh_command(ssh, placement[i][0], os.getcwd(), keep, cmd)
+        return subprocess.Popen(argv, env=wenv, **kw)
+
+    def start_standby(i):
+        with lock:
+            fifo_count[0] += 1
+            path = os.path.join(fifo_dir, "task%d.%d" % (i, fifo_count[0]))
+        os.mkfifo(path)
+        return start(i, 0, fifo=path), path
+
+    def release(spare, attempt):
+        """hand a waiting standby process the life of its task; False if it is gone"""
+        proc, path = spare
+        if proc.poll() is not None:
+            return False
+        try:
+            # (opening blocks until the standby has reached rabit::Init and opened its end)
+            with open(path, "w") as fo:
+                fo.write("%d\n" % attempt)
+            return True
+        except OSError:
+            return False
+
+    def discard(spare):
+        proc, path = spare
+        if proc.poll() is None:
+            proc.kill()
+        try:
+            proc.communicate(timeout=10)
+        except Exception:  # pylint: disable=broad-except
+            pass
+        try:
+            os.remove(path)
+        except OSError:
+            pass
+
     def run_task(i):
         attempt = 0
         chunks = []
+        spare = None
+        p = None
         while True:
-            wenv = dict(os.environ)
-            if env:
-                wenv.update(env)
-            wenv.update(tracker.worker_env())
-            wenv["DMLC_TASK_ID"] = str(i)
-            wenv["DMLC_NUM_ATTEMPT"] = str(attempt)
-            local = i if placement is None else placement[i][1]
-            wenv["RABIT_LOCAL_RANK"] = str(local)
-            if per_rank_gpu:
-                wenv["RABIT_DEVICE_ORDINAL"] = str(local)
-            kw = {}
-            if capture:
-                kw = dict(stdout=subprocess.PIPE, stderr=subprocess.STDOUT)
-            argv = cmd
-            if placement is not None:
-                # only what the job needs travels: the launcher's own environment stays here
-                keep = dict((k, v) for k, v in wenv.items()
-                            if k.startswith(("DMLC_", "RABIT_", "rabit_")) or (env and k in env))
-                argv = ssh_command(ssh, placement[i][0], os.getcwd(), keep, cmd)
-            p = subprocess.Popen(argv, env=wenv, **kw)
+            if p is None:
+                p = start(i, attempt)
+            if use_standby and spare is None:
+                spare = start_standby(i)
             with lock:
                 procs[i] = p
             try:
@@ -135,6 +189,19 @@ def launch(cmd, nworker, max_attempts=20, env=None, capture=False, timeout=None,
             if rc == 0 or attempt >= max_attempts:
                 break
             attempt += 1
+            p = None
+            if spare is not None:
+                if release(spare, attempt):
+                    p = spare[0]
+                    try:
+                        os.remove(spare[1])
+                    except OSError:
+                        pass
+                else:
+                    discard(spare)
+                spare = None
+        if spare is not None:
+            discard(spare)
         with lock:
             res.returncodes[i] = rc
             res.attempts[i] = attempt
@@ -147,6 +214,11 @@ def launch(cmd, nworker, max_attempts=20, env=None, capture=False, timeout=None,
     for t in threads:
         t.join()
     res.wall = time.time() - t0
+    if fifo_dir is not None:
+        try:
+            os.rmdir(fifo_dir)
+        except OSError:
+            pass
     if res.ok:
         tracker.join(5.0)
     tracker.close()
@@ -159,6 +231,8 @@ def main():
     ap.add_argument("-n", "--num-workers", type=int, required=True)
     ap.add_argument("--max-attempts", "--local-num-attempt", type=int, default=20, dest="max_attempts")
     ap.add_argument("--gpus", action="store_true", help="bind task i to GPU i")
+    ap.add_argument("--standby", action="store_true",
+                    help="keep a pre-started process per task that takes over when the worker dies (fast recovery)")
     ap.add_argument("--timeout", type=float, default=None)
     ap.add_argument("--cluster", choices=["local", "ssh"], default="local")
     ap.add_argument("--host-file", help="ssh cluster: one host[:slots] per line")
@@ -174,7 +248,7 @@ def main():
             ap.error("--cluster ssh needs --host-file")
         hosts = read_host_file(args.host_file)
     res = launch(cmd, args.num_workers, max_attempts=args.max_attempts, timeout=args.timeout,
-                 per_rank_gpu=args.gpus, verbose=True, host=args.tracker_host, hosts=hosts)
+                 per_rank_gpu=args.gpus, verbose=True, host=args.tracker_host, hosts=hosts, standby=args.standby)
     if not res.ok:
         print("launcher: some workers failed: %r" % res.returncodes, file=sys.stderr)
     sys.exit(0 if res.ok else 1)

@@ -72,7 +72,7 @@ __device__ __forceinline__ void StreamP2PBody(const Params &p, const StreamArgs 
   char *keep = static_cast<char *>(p.keep[ix]);
   const bool aligned = (reinterpret_cast<uintptr_t>(user) % kVec) == 0;
   Stamp(p, 0);
-  int verdict = FlagBarrier(p, me, EntryRow{OpEpoch(p) & 1u}, OpEpoch(p) + 1, p.code[ix], true, &s_verdict);
+  int verdict = FlagBarrier(p, me, EntryRow{OpEpoch(p) & 1u}, OpEpoch(p) + 1, p.code[ix], true, &s_verdict, false);
   if (verdict != kStOk) { Report(p, me, verdict); return; }
   Stamp(p, 2);
   const size_t nvec_full = p.bytes / kVec;
@@ -141,7 +141,7 @@ __device__ __forceinline__ void StreamP2PBody(const Params &p, const StreamArgs 
     }
   }
   // a peer may still be pulling from OUR result region: nobody leaves (and lets the next op write into it) early
-  verdict = FlagBarrier(p, me, ExitRow{}, OpEpoch(p) + 1, 0u, false, &s_verdict);
+  verdict = FlagBarrier(p, me, ExitRow{}, OpEpoch(p) + 1, 0u, false, &s_verdict, false);
   if (verdict != kStOk) { Report(p, me, verdict); return; }
   Stamp(p, 5);
 }
@@ -163,7 +163,7 @@ __device__ __forceinline__ void StreamNvlsBody(const Params &p, const StreamArgs
   char *keep = static_cast<char *>(p.keep[0]);
   const bool aligned = (reinterpret_cast<uintptr_t>(user) % kVec) == 0;
   Stamp(p, 0);
-  int verdict = FlagBarrier(p, me, EntryRow{OpEpoch(p) & 1u}, OpEpoch(p) + 1, p.code[0], true, &s_verdict);
+  int verdict = FlagBarrier(p, me, EntryRow{OpEpoch(p) & 1u}, OpEpoch(p) + 1, p.code[0], true, &s_verdict, false);
   if (verdict != kStOk) { Report(p, me, verdict); return; }
   Stamp(p, 2);
   const size_t nvec_full = p.bytes / kVec;

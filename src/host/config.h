@@ -62,9 +62,9 @@ struct Config {
   size_t device_oneshot_max = 512 << 10;     // bytes: <= -> one-shot kernel
   size_t device_nvls_min = 0;                // bytes: >= -> multimem kernel when available; 0 = table by world size
   size_t device_ll_max = 0;                  // bytes: <= -> tagged-word kernel; 0 = table by world size
-  size_t device_stream_min = 0;              // bytes: >= -> chunked, copy-engine fed allreduce; 0 = table (32 MiB)
-  size_t device_stream_chunk = 0;            // bytes per chunk of that path; 0 = table (64 MiB)
-  size_t device_stream_first = 0;            // bytes of its first chunk; 0 = table (8 MiB)
+  size_t device_stream_min = 0;              // bytes: >= -> chunked, copy-engine fed allreduce; 0 = table (128 MiB)
+  size_t device_stream_chunk = 0;            // bytes per chunk of that path; 0 = table (512 MiB)
+  size_t device_stream_first = 0;            // bytes of its first chunk; 0 = table (64 MiB)
   std::string device_tune = "";              // file with measured thresholds (benchmarks/algo_sweep.py --emit-table)
   int device_blocks = 0;                     // 0 = table default
   int device_timeout_ms = 20000;             // bounded spin before a peer is declared dead
@@ -73,7 +73,7 @@ struct Config {
   size_t device_cache_bytes = 16UL << 30;    // device-resident result cache budget
   size_t device_blob_min = 32UL << 10;       // bytes: recovery payloads / checkpoint replicas >= this move by NVLink peer copies
   size_t device_host_min = 4UL << 20;        // bytes: HOST buffers >= this ride PCIe + NVLink instead of TCP; 0 = off
-  size_t device_host_chunk = 32UL << 20;     // pipeline granule of that path (H2D | kernel | D2H overlap)
+  size_t device_host_chunk = 64UL << 20;     // pipeline granule of that path (H2D | kernel | D2H overlap)
 
   /*! \brief names looked up in the environment at Init */
   static const std::vector<std::string> &EnvNames() {

@@ -45,6 +45,19 @@ bool BaseEngine::Init(int argc, char *argv[]) {
     exit(0);
   }
   comm_.host = utils::SockAddr::GetHostName();
+  // Standby worker (started by the launcher next to the live one, RABIT_STANDBY_FIFO): everything up to here - the
+  // program's own start-up, library loading, and now the CUDA context - is done ahead of time; the process then
+  // sleeps until the launcher hands it the life of a worker that died (one line: the attempt number) or ends the
+  // job (end of file). Cuts the dominant part of recover-after-kill: starting a process and its CUDA context.
+  if (const char *fifo = getenv("RABIT_STANDBY_FIFO")) {
+    if (comm_.cfg.device != "off") device_.reset(DeviceBackend::Create(comm_.cfg));
+    FILE *f = fopen(fifo, "r");
+    int attempt = 0;
+    if (f == nullptr || fscanf(f, "%d", &attempt) != 1) exit(0);   // the job ended without needing us
+    fclose(f);
+    comm_.cfg.num_trial = attempt;
+    unsetenv("RABIT_STANDBY_FIFO");
+  }
   if (!comm_.Connect("start")) {
     if (comm_.job_over) {
       // A replacement process that arrives after its peers have left: they could only leave because every rank,
@@ -59,13 +72,15 @@ bool BaseEngine::Init(int argc, char *argv[]) {
   }
   if (comm_.world > 1 || comm_.cfg.device_force) {
     const double t_dev = utils::GetTime();
-    device_.reset(DeviceBackend::Create(comm_.cfg));
+    if (!device_) device_.reset(DeviceBackend::Create(comm_.cfg));
     if (getenv("RABIT_RECOVER_PROFILE") != nullptr) {
       utils::HandleLogInfo("[%d] init: CUDA context + backend set-up %.1f ms (attempt %d)\n", comm_.rank,
                            (utils::GetTime() - t_dev) * 1e3, comm_.cfg.num_trial);
     }
     // (a link that breaks this early is fatal here; the robust engine re-joins instead, see RobustEngine::Init)
     utils::Check(this->AttachDevice() != AttachResult::kLinkError, "lost a peer while setting up the device arena");
+  } else {
+    device_.reset();
   }
   initialized_ = true;
   return true;

@@ -51,3 +51,28 @@ def test_ssh_cluster_local_rank_is_per_host(tmp_path):
                  hosts=[("nodeA", 2), ("nodeB", 2)], ssh=(ssh,), per_rank_gpu=True)
     got = sorted(line for o in res.outputs.values() for line in o.splitlines() if line.startswith("LR"))
     assert got == ["LR 0 0 0", "LR 1 1 1", "LR 2 0 0"]
+
+
+def test_standby_workers_take_over(built):
+    """--standby: a pre-started process waits inside rabit::Init and is handed the life of a worker that died, also
+    twice in a row for the same task; standbys that were never needed end with the job"""
+    res = launch([bin_path("model_recover"), "3000", "rabit_bootstrap_cache=1", "mock=0,0,1,0", "mock=1,1,1,0", "mock=1,1,1,1",
+                  "mock=3,2,1,0"], 4, capture=True, timeout=120, standby=True)
+    assert res.ok, res.outputs
+    assert res.restarts == 4
+    assert sorted(res.attempts.values()) == [0, 1, 1, 2]
+
+
+def test_standby_python_worker_sees_attempt_number():
+    code = ("import sys\nfrom rabit_b200 import rabit\nimport numpy as np\n"
+            "rabit.init(sys.argv, lib='mock')\n"
+            "v, m = rabit.load_checkpoint()\n"
+            "for it in range(v, 2):\n"
+            "    a = rabit.allreduce(np.ones(4, dtype=np.float32), rabit.SUM)\n"
+            "    assert a[0] == rabit.get_world_size()\n"
+            "    rabit.checkpoint(it)\n"
+            "rabit.finalize()\n")
+    env = {"PYTHONPATH": ROOT + os.pathsep + os.environ.get("PYTHONPATH", "")}
+    res = launch([sys.executable, "-c", code, "mock=1,1,0,0"], 3, capture=True, timeout=120, standby=True, env=env)
+    assert res.ok, res.outputs
+    assert res.restarts == 1
