@@ -10,6 +10,7 @@ Outputs (all git-ignored, all travel to the GPU box with the gpurun snapshot):
     lib/librabit_mock.so   default engine: mock        (reference librabit_mock)
     lib/librabit_base.so   default engine: base        (reference librabit_base)
     lib/librabit_empty.so  default engine: empty       (reference librabit_empty)
+    lib/librabit_nccl.so   default engine: nccl        (the library-backed comparator; reference librabit_mpi)
     build/bin/*            guide + test programs (basic, broadcast, lazy_allreduce,
                            model_recover, local_recover, lazy_recover, speed_test, ...)
 
@@ -30,7 +31,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 HOST_SRCS = ["comm", "engine_base", "engine_robust", "engine_recover", "engine_ops",
              "engine_mock", "result_store", "c_api"]
 ENGINES = {"librabit.so": "robust", "librabit_mock.so": "mock",
-           "librabit_base.so": "base", "librabit_empty.so": "empty"}
+           "librabit_base.so": "base", "librabit_empty.so": "empty", "librabit_nccl.so": "nccl"}
 CXXFLAGS = ["-std=c++17", "-O3", "-g", "-Wall", "-fPIC", "-pthread", "-I" + os.path.join(ROOT, "include")]
 NVCC_ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 

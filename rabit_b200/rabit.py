@@ -37,8 +37,10 @@ DTYPE_ENUM__ = {
     np.dtype("float64"): 7,
 }
 
+# 'mpi' names the library-backed, non-fault-tolerant engine: MPI in the reference (python/rabit.py:47-71,
+# librabit_mpi), NCCL here (src/device/engine_nccl.cu); 'nccl' is the same library under its own name
 _LIB_NAMES = {"standard": "librabit.so", "mock": "librabit_mock.so", "base": "librabit_base.so",
-              "empty": "librabit_empty.so", "mpi": "librabit_base.so"}
+              "empty": "librabit_empty.so", "mpi": "librabit_nccl.so", "nccl": "librabit_nccl.so"}
 
 
 def lib_dir():
@@ -81,7 +83,7 @@ def _loadlib(lib="standard", lib_dll=None):
         _LIB = lib_dll
     else:
         if lib not in _LIB_NAMES:
-            raise ValueError("unknown rabit lib %r (standard|mock|base|empty)" % (lib,))
+            raise ValueError("unknown rabit lib %r (standard|mock|base|empty|mpi|nccl)" % (lib,))
         path = os.path.join(lib_dir(), _LIB_NAMES[lib])
         if not os.path.isfile(path):
             raise RuntimeError("cannot find %s; run `python build.py` in the repository root" % path)
@@ -106,7 +108,8 @@ def init(args=None, lib="standard", lib_dll=None):
     """Start the engine.
 
     args: list of ``name=value`` strings (str or bytes); None means ``sys.argv``.
-    lib: 'standard' (robust engine), 'mock' (fault injection), 'base', 'empty'.
+    lib: 'standard' (robust engine), 'mock' (fault injection), 'base', 'empty', 'mpi' / 'nccl' (library-backed
+    comparator engine, not fault tolerant; needs the CUDA build).
     """
     if args is None:
         args = sys.argv

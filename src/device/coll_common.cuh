@@ -312,6 +312,15 @@ __device__ __forceinline__ void Stamp(const Params &p, int idx) {
   if (p.trace != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) p.trace[idx] = GlobalTimer();
 }
 
+/*!
+ * \brief which rank reduces the k-th tile of this block's channel. Offset by the channel number: a message of no
+ *  more tiles than blocks gives every block exactly one tile (k = 0), and without the offset rank 0 would own,
+ *  i.e. reduce and re-distribute, ALL of them while the other GPUs wait (256 KiB - 4 MiB messages).
+ */
+__device__ __forceinline__ int TileOwner(size_t k, int n) {
+  return static_cast<int>((k + blockIdx.x) % static_cast<size_t>(n));
+}
+
 // ------------------------------------------------------------------ reduce ops
 struct OpMax { template <typename T> __device__ __forceinline__ static T Apply(T a, T b) { return a < b ? b : a; } };
 struct OpMin { template <typename T> __device__ __forceinline__ static T Apply(T a, T b) { return b < a ? b : a; } };

@@ -48,7 +48,7 @@ __device__ __forceinline__ void TwoShotInPlaceBody(const Params &p) {
   const size_t ntiles = (nvec + tile_vecs - 1) / tile_vecs;
   const int n = p.world;
   for (size_t tile = blockIdx.x, k = 0; tile < ntiles; tile += gridDim.x, ++k) {
-    if (static_cast<int>(k % n) != me) continue;
+    if (TileOwner(k, n) != me) continue;
     const size_t v0 = tile * tile_vecs + threadIdx.x;
     uint4 acc[kUnroll];
 #pragma unroll
@@ -84,7 +84,7 @@ __device__ __forceinline__ void TwoShotInPlaceBody(const Params &p) {
   if (verdict != kStOk) { Report(p, me, verdict); return; }
   Stamp(p, 4);
   for (size_t tile = blockIdx.x, k = 0; tile < ntiles; tile += gridDim.x, ++k) {
-    const int owner = static_cast<int>(k % n);
+    const int owner = TileOwner(k, n);
     if (owner == me) continue;
     const char *src = SymOf(p, owner);
     const size_t v0 = tile * tile_vecs + threadIdx.x;
@@ -134,7 +134,7 @@ __device__ __forceinline__ void NvlsInPlaceBody(const Params &p) {
   const size_t ntiles = (nvec + tile_vecs - 1) / tile_vecs;
   const int n = p.world;
   for (size_t tile = blockIdx.x, k = 0; tile < ntiles; tile += gridDim.x, ++k) {
-    if (static_cast<int>(k % n) != me) continue;
+    if (TileOwner(k, n) != me) continue;
     const size_t v0 = tile * tile_vecs + threadIdx.x;
     uint4 acc[kNvlsUnroll];
 #pragma unroll

@@ -138,9 +138,9 @@ __device__ __forceinline__ void TwoShotAllreduceBody(const Params &p) {
   const size_t ntiles = (nvec + tile_vecs - 1) / tile_vecs;
   const int n = p.world;
   char *my_stage = StageOf(p, me);
-  // reduce-scatter: the k-th tile of this channel is owned by rank k % n
+  // reduce-scatter: the k-th tile of this channel is owned by rank TileOwner(k, n)
   for (size_t tile = blockIdx.x, k = 0; tile < ntiles; tile += gridDim.x, ++k) {
-    if (static_cast<int>(k % n) != me) continue;
+    if (TileOwner(k, n) != me) continue;
     const size_t v0 = tile * tile_vecs + threadIdx.x;
     uint4 acc[kUnroll];
 #pragma unroll
@@ -175,7 +175,7 @@ __device__ __forceinline__ void TwoShotAllreduceBody(const Params &p) {
   Stamp(p, 4);
   // allgather: pull every tile from its owner's stage
   for (size_t tile = blockIdx.x, k = 0; tile < ntiles; tile += gridDim.x, ++k) {
-    const char *src = StageOf(p, static_cast<int>(k % n));
+    const char *src = StageOf(p, TileOwner(k, n));
     const size_t v0 = tile * tile_vecs + threadIdx.x;
     uint4 r[kUnroll];
 #pragma unroll

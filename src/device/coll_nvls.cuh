@@ -99,7 +99,7 @@ __device__ __forceinline__ void NvlsAllreduceBody(const Params &p) {
   const int n = p.world;
   char *mc_stage = McStage(p);
   for (size_t tile = blockIdx.x, k = 0; tile < ntiles; tile += gridDim.x, ++k) {
-    if (static_cast<int>(k % n) != me) continue;
+    if (TileOwner(k, n) != me) continue;
     const size_t v0 = tile * tile_vecs + threadIdx.x;
     uint4 acc[kUnroll];
 #pragma unroll

@@ -81,9 +81,9 @@ __device__ __forceinline__ void StreamP2PBody(const Params &p, const StreamArgs 
   const size_t ntiles = (nvec + tile_vecs - 1) / tile_vecs;
   const int n = p.world;
   char *my_res = p.arena[me] + a.res_off;
-  // reduce-scatter: the k-th tile of this channel is owned by rank k % n
+  // reduce-scatter: the k-th tile of this channel is owned by rank TileOwner(k, n)
   for (size_t tile = blockIdx.x, k = 0; tile < ntiles; tile += gridDim.x, ++k) {
-    if (static_cast<int>(k % n) != me) continue;
+    if (TileOwner(k, n) != me) continue;
     const size_t v0 = tile * tile_vecs + threadIdx.x;
     uint4 acc[kUnroll];
 #pragma unroll
@@ -121,7 +121,7 @@ __device__ __forceinline__ void StreamP2PBody(const Params &p, const StreamArgs 
   Stamp(p, 4);
   // allgather: pull every tile this rank does not own from its owner's result region
   for (size_t tile = blockIdx.x, k = 0; tile < ntiles; tile += gridDim.x, ++k) {
-    const int owner = static_cast<int>(k % n);
+    const int owner = TileOwner(k, n);
     if (owner == me) continue;
     const char *src = p.arena[owner] + a.res_off;
     const size_t v0 = tile * tile_vecs + threadIdx.x;
@@ -174,7 +174,7 @@ __device__ __forceinline__ void StreamNvlsBody(const Params &p, const StreamArgs
   const char *mc_src = p.mc_arena + a.src_off;
   char *mc_res = p.mc_arena + a.res_off;
   for (size_t tile = blockIdx.x, k = 0; tile < ntiles; tile += gridDim.x, ++k) {
-    if (static_cast<int>(k % n) != me) continue;
+    if (TileOwner(k, n) != me) continue;
     const size_t v0 = tile * tile_vecs + threadIdx.x;
     uint4 acc[kNvlsUnroll];
 #pragma unroll

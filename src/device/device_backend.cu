@@ -34,6 +34,7 @@
 #include "coll_inplace.cuh"
 #include "coll_stream.cuh"
 #include "coll_blob.cuh"
+#include "coll_gather.cuh"
 #include "coll_ll.cuh"
 #include "device_backend.h"
 #include "../host/engine_core.h"

@@ -167,3 +167,31 @@ def test_cuda_graph_replay_across_ranks(world):
     """collectives captured in a CUDA graph and replayed on every rank (device-side op epoch)"""
     res = _run(["20000", "iters=2", "graph=1"], world, timeout=600)
     assert res.ok, {i: o[-2500:] for i, o in res.outputs.items()}
+
+
+def test_nccl_engine_as_comparator(world):
+    """rabit_engine=nccl (python lib='mpi'): the library-backed, non-fault-tolerant engine, the counterpart of the
+    reference's MPI engine; device tensors go to ncclAllReduce / ncclBroadcast, host arrays to the TCP collectives"""
+    code = ("import os, sys\nimport numpy as np\nimport torch\n"
+            "from rabit_b200 import rabit\nfrom rabit_b200 import torch_binding as rt\n"
+            "torch.cuda.set_device(int(os.environ['RABIT_DEVICE_ORDINAL']) % torch.cuda.device_count())\n"
+            "rabit.init(sys.argv, lib='mpi')\n"
+            "me, n = rabit.get_rank(), rabit.get_world_size()\n"
+            "x = torch.full((100003,), float(me + 1), device='cuda')\n"
+            "rabit.allreduce(x, rabit.SUM)\n"
+            "assert torch.equal(x, torch.full_like(x, n * (n + 1) / 2)), 'nccl allreduce'\n"
+            "y = torch.arange(5000, device='cuda', dtype=torch.int32) * (me + 1)\n"
+            "rabit.allreduce(y, rabit.MAX)\n"
+            "assert torch.equal(y, torch.arange(5000, device='cuda', dtype=torch.int32) * n), 'nccl max'\n"
+            "b = torch.full((70001,), me, dtype=torch.uint8, device='cuda')\n"
+            "rt.broadcast_(b, n - 1)\n"
+            "assert torch.equal(b, torch.full_like(b, n - 1)), 'nccl broadcast'\n"
+            "h = rabit.allreduce(np.full(10, me, dtype=np.float64), rabit.SUM)\n"
+            "assert h[0] == n * (n - 1) / 2\n"
+            "assert not rt.device_active()\n"
+            "rabit.tracker_print('[%d] nccl engine ok\\n' % me)\n"
+            "rabit.finalize()\n")
+    env = {"PYTHONPATH": ROOT + os.pathsep + os.environ.get("PYTHONPATH", "")}
+    res = run_job([sys.executable, "-c", code], world, timeout=300, env=env, per_rank_gpu=True)
+    assert res.ok, {i: o[-2000:] for i, o in res.outputs.items()}
+    assert sum("nccl engine ok" in m for m in res.messages) == world

@@ -70,3 +70,20 @@ rabit.finalize()
     res = run_py(code, 3)
     assert res.ok, res.outputs
     assert sum("fine" in m for m in res.messages) == 3
+
+
+def test_lib_mpi_selects_the_library_backed_engine():
+    """lib='mpi' (reference python/rabit.py:47-71 -> librabit_mpi) loads the library-backed engine of this build,
+    librabit_nccl.so; a world of one needs neither NCCL nor a GPU"""
+    code = ("from rabit_b200 import rabit\nimport numpy as np, os\n"
+            "rabit.init(['prog'], lib='mpi')\n"
+            "assert os.path.basename(rabit._LIB_PATH) == 'librabit_nccl.so', rabit._LIB_PATH\n"
+            "a = rabit.allreduce(np.arange(4, dtype=np.float32), rabit.SUM)\n"
+            "assert a.tolist() == [0, 1, 2, 3]\n"
+            "assert rabit.get_world_size() == 1\n"
+            "rabit.finalize()\nprint('mpi-lib-ok')\n")
+    import subprocess
+    import sys
+    env = dict(os.environ, PYTHONPATH=ROOT)
+    r = subprocess.run([sys.executable, "-c", code], env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, timeout=120)
+    assert r.returncode == 0 and b"mpi-lib-ok" in r.stdout, r.stdout.decode()
