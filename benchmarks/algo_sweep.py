@@ -4,6 +4,10 @@
 
     python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29720 \
         benchmarks/algo_sweep.py [--sizes 4194304,268435456] [--algos twoshot,tma,nvls] [--blocks 0,74,148,296]
+
+    ... benchmarks/algo_sweep.py --emit-table profiles/dispatch_table.txt
+        sweeps 1 KiB - 4 MiB over {ll, oneshot, twoshot, nvls} and appends the measured thresholds of this world
+        size as lines "world key value" (the format the backend reads: rabit_device_tune=<file>)
 """
 import argparse
 import json
@@ -27,14 +31,20 @@ def main():
     ap.add_argument("--iters", type=int, default=10)
     ap.add_argument("--out", default="")
     ap.add_argument("--sym", action="store_true", help="operate on a symmetric (zero-copy) buffer")
+    ap.add_argument("--emit-table", default="", help="append the measured dispatch thresholds of this world size to this file")
     args = ap.parse_args()
+    if args.emit_table:
+        args.sizes = ",".join(str(1 << k) for k in range(10, 23))
+        args.algos = "ll,oneshot,twoshot,nvls"
+        args.blocks = "0"
+        args.iters = max(args.iters, 20)
     rank, world, local = bench.dist_env()
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     store = bench.make_store(rank, world)
     tracker, port = bench.start_tracker(rank, world, store)
     sizes = [int(s) for s in args.sizes.split(",")]
-    init = ["rabit_device=on", "rabit_device_arena=%d" % (2 * max(sizes) + (4 << 20))]
+    init = ["rabit_device=on", "rabit_device_arena=%d" % (2 * max(sizes) + (4 << 20)), "rabit_device_stream_min=64G"]
     if args.sym:
         init += ["rabit_device_heap=%d" % (max(sizes) + (1 << 20))]
     if world > 1:
@@ -53,6 +63,8 @@ def main():
         v = x[:sz // 4]
         for algo in args.algos.split(","):
             if algo == "oneshot" and sz > (8 << 20):
+                continue
+            if algo == "ll" and sz > 32768:
                 continue
             for blocks in [int(b) for b in args.blocks.split(",")]:
                 rt.set_tuning(algo, blocks, trace=False)
@@ -93,6 +105,26 @@ def main():
     rt.set_tuning("auto", 0, False)
     desc = rt.describe()
     rabit.finalize()
+    if rank == 0 and args.emit_table:
+        best = {}
+        for r in rows:
+            if r["correct"] and (r["bytes"] not in best or r["us"] < best[r["bytes"]][1]):
+                best[r["bytes"]] = (r["algo"], r["us"])
+        by = sorted(best)
+        ll_max = max([b for b in by if best[b][0] == "ll"] or [0])
+        # nvls from the first size after which it never loses again
+        nvls_min = None
+        for b in reversed(by):
+            if best[b][0] == "nvls":
+                nvls_min = b
+            else:
+                break
+        with open(args.emit_table, "a") as fo:
+            fo.write("# world %d: winners %s\n" % (n, " ".join("%d:%s:%.1fus" % (b, best[b][0], best[b][1]) for b in by)))
+            fo.write("%d ll_max %d\n" % (n, ll_max))
+            if nvls_min is not None:
+                fo.write("%d nvls_min %d\n" % (n, nvls_min))
+        print("TABLE world %d ll_max %d nvls_min %s" % (n, ll_max, nvls_min))
     if rank == 0:
         print(desc)
         if args.out:

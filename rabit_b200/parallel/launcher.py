@@ -141,15 +141,21 @@ def launch(cmd, nworker, max_attempts=20, env=None, capture=False, timeout=None,
         if proc.poll() is not None:
             return False
         try:
-            # (opening blocks until the standby has reached rabit::Init and opened its end)
-            with open(path, "w") as fo:
-                fo.write("%d\n" % attempt)
+            fd = spare_fds.pop(path, None)
+            if fd is None:
+                # (opening blocks until the standby has reached rabit::Init and opened its end)
+                fd = os.open(path, os.O_WRONLY)
+            os.write(fd, ("%d\n" % attempt).encode())
+            os.close(fd)
             return True
         except OSError:
             return False
 
     def discard(spare):
         proc, path = spare
+        fd = spare_fds.pop(path, None)
+        if fd is not None:
+            os.close(fd)
         if proc.poll() is None:
             proc.kill()
         try:
@@ -161,10 +167,35 @@ def launch(cmd, nworker, max_attempts=20, env=None, capture=False, timeout=None,
         except OSError:
             pass
 
+    def parked(spare):
+        """has this standby reached rabit::Init and opened its fifo? (a non-blocking open for writing succeeds
+        only once a reader is there)"""
+        proc, path = spare
+        if proc.poll() is not None:
+            return True
+        try:
+            fd = os.open(path, os.O_WRONLY | os.O_NONBLOCK)
+        except OSError:
+            return False
+        # keep the write end open until release(): closing it now would look like "job over" to the standby
+        spare_fds[path] = fd
+        return True
+
+    spare_fds = {}
+    first_spares = {}
+    if use_standby:
+        # steady state from the first second on: the standbys are started (and have their CUDA context) before the
+        # job itself, so that an early death already finds a warm replacement
+        for i in range(nworker):
+            first_spares[i] = start_standby(i)
+        t_warm = time.time()
+        while time.time() - t_warm < 120 and not all(parked(sp) for sp in first_spares.values() if sp[1] not in spare_fds):
+            time.sleep(0.02)
+
     def run_task(i):
         attempt = 0
         chunks = []
-        spare = None
+        spare = first_spares.get(i)
         p = None
         while True:
             if p is None:

@@ -32,7 +32,12 @@ __device__ __forceinline__ void StoreVecAny(char *ptr, const uint4 &v, bool alig
   for (int k = 0; k < kVec; ++k) ptr[k] = s[k];
 }
 
-__device__ __forceinline__ void AllgatherMcBody(const Params &p) {
+/*!
+ * \brief inplace != 0: the buffer is symmetric (same arena offset on every rank, p.sym_offset): every rank multicasts
+ *  its range straight into everybody's BUFFER. No stage, no header, no copy-out: each byte crosses NVLink once and
+ *  is written once. (Ragged range edges still go byte-wise into every peer.)
+ */
+__device__ __forceinline__ void AllgatherMcBody(const Params &p, int inplace) {
   __shared__ int s_verdict;
   const int me = p.rank, n = p.world;
   char *user = static_cast<char *>(p.user[0]);
@@ -40,9 +45,39 @@ __device__ __forceinline__ void AllgatherMcBody(const Params &p) {
   const size_t begin = p.slice_begin[0], end = p.slice_end[0];
   const bool aligned = (reinterpret_cast<uintptr_t>(user) % kVec) == 0;
   const size_t tile_vecs = static_cast<size_t>(blockDim.x) * kUnroll;
-  // nobody may still be reading the previous contents of the stages
+  // nobody may still be reading the previous contents of the stages (or, in place, of its buffer)
   int verdict = FlagBarrier(p, me, EntryRow{OpEpoch(p) & 1u}, OpEpoch(p) + 1, p.code[0], true, &s_verdict, false);
   if (verdict != kStOk) { Report(p, me, verdict); return; }
+  if (inplace) {
+    char *mc_buf = p.mc_arena + p.sym_offset;
+    if (begin < end) {
+      const size_t vb = begin / kVec, ve = (end + kVec - 1) / kVec;
+      const size_t ntiles = (ve - vb + tile_vecs - 1) / tile_vecs;
+      for (size_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+          const size_t v = vb + tile * tile_vecs + threadIdx.x + static_cast<size_t>(u) * blockDim.x;
+          if (v >= ve) continue;
+          const size_t b0 = v * kVec, b1 = b0 + kVec;
+          if (b0 >= begin && b1 <= end) {
+            MultimemStore(mc_buf + b0, LoadVec(user + b0));   // symmetric buffers are 256-byte aligned
+          } else {
+            const size_t e0 = b0 > begin ? b0 : begin, e1 = b1 < end ? b1 : end;
+            for (size_t i = e0; i < e1; ++i) {
+              const char c = user[i];
+              for (int r = 0; r < n; ++r) if (r != me) (p.arena[r] + p.sym_offset)[i] = c;
+            }
+          }
+        }
+      }
+    }
+    verdict = FlagBarrier(p, me, MidRow{}, OpEpoch(p) + 1, 0u, false, &s_verdict);
+    if (verdict != kStOk) { Report(p, me, verdict); return; }
+    // (A result-cache copy is NOT taken here: a block only knows that the tiles pushed by the peers' same-numbered
+    // blocks are complete, and the peers' ranges are not known in this variant. The host enqueues a device copy of
+    // the whole buffer behind this kernel instead.)
+    return;
+  }
   char *mc = McStage(p);
   if (threadIdx.x == 0) {
     // every block announces the range (same words): a peer's block b learns it through ITS barrier with our block b
@@ -114,10 +149,10 @@ __device__ __forceinline__ void AllgatherMcBody(const Params &p) {
   }
 }
 /*! \brief launch wrapper: epoch from the control block (BeginOp), body, completion count (EndOp) */
-__global__ void __launch_bounds__(512) AllgatherMc(Params p) {
+__global__ void __launch_bounds__(512) AllgatherMc(Params p, int inplace) {
   const int me = p.emulate ? blockIdx.y : p.rank;
   BeginOp(p, me);
-  AllgatherMcBody(p);
+  AllgatherMcBody(p, inplace);
   EndOp(p, me);
 }
 
