@@ -34,7 +34,7 @@ def main():
     ap.add_argument("--emit-table", default="", help="append the measured dispatch thresholds of this world size to this file")
     args = ap.parse_args()
     if args.emit_table:
-        args.sizes = ",".join(str(1 << k) for k in range(10, 23))
+        args.sizes = ",".join(str(1 << k) for k in range(10, 27))
         args.algos = "ll,oneshot,twoshot,nvls"
         args.blocks = "0"
         args.iters = max(args.iters, 20)
@@ -119,9 +119,13 @@ def main():
                 nvls_min = b
             else:
                 break
+        # one-shot vs two-shot among the sizes the switch does not take
+        t = dict(((r["bytes"], r["algo"]), r["us"]) for r in rows if r["correct"])
+        oneshot_max = max([b for b in by if (b, "oneshot") in t and t[(b, "oneshot")] <= t.get((b, "twoshot"), 1e30)] or [0])
         with open(args.emit_table, "a") as fo:
             fo.write("# world %d: winners %s\n" % (n, " ".join("%d:%s:%.1fus" % (b, best[b][0], best[b][1]) for b in by)))
             fo.write("%d ll_max %d\n" % (n, ll_max))
+            fo.write("%d oneshot_max %d\n" % (n, oneshot_max))
             if nvls_min is not None:
                 fo.write("%d nvls_min %d\n" % (n, nvls_min))
         print("TABLE world %d ll_max %d nvls_min %s" % (n, ll_max, nvls_min))

@@ -6,7 +6,7 @@ N=${1:-8}
 TAG=${2:-g$N}
 OUT=gpurun_out
 mkdir -p $OUT
-echo "== tests"; timeout 900 python -m pytest tests/test_gpu_multi.py -x -q -k "(no_fault and auto) or streamed_allreduce_no_fault or 1,2,2 or 0,2,6 or local_models or recovery_after_kills or host_buffers or nccl_engine or zero_copy or lazy_checkpoint" > $OUT/${TAG}_tests.log 2>&1; echo "tests rc=$?" >> $OUT/${TAG}_tests.log; tail -4 $OUT/${TAG}_tests.log | cut -c1-600
+echo "== tests"; timeout 900 python -m pytest tests/test_gpu_multi.py -x -q -k "(no_fault and auto) or streamed_allreduce_no_fault or death_inside or local_models or recovery_after_kills or host_buffers or nccl_engine or zero_copy or lazy_checkpoint" > $OUT/${TAG}_tests.log 2>&1; echo "tests rc=$?" >> $OUT/${TAG}_tests.log; tail -4 $OUT/${TAG}_tests.log | cut -c1-600
 echo "== chunk plans"; for p in 64M:512M 512M:512M 32M:128M; do timeout 120 python -m rabit_b200.parallel.launcher -n $N --gpus python benchmarks/stream_diag.py plans=$p mib=256 2>&1 | grep DIAG; done > $OUT/${TAG}_plans.log; cut -c1-500 $OUT/${TAG}_plans.log
 echo "== dispatch table"; timeout 200 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29531 benchmarks/algo_sweep.py --emit-table $OUT/${TAG}_dispatch.txt > $OUT/${TAG}_sweep.log 2>&1; grep TABLE $OUT/${TAG}_sweep.log; cat $OUT/${TAG}_dispatch.txt | cut -c1-700
 echo "== bench ours"; timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29532 bench.py --gpus $N --steps 20 --warmup 5 > $OUT/${TAG}_bench.json 2> $OUT/${TAG}_bench.err; echo "bench rc=$?"; grep -i "error\|assert" $OUT/${TAG}_bench.err | head -5

@@ -59,7 +59,7 @@ struct Config {
   std::string device = "auto";               // auto|on|off
   size_t device_arena = 0;                   // bytes of symmetric staging; 0 = grow on demand
   size_t device_heap = 0;                    // bytes of symmetric heap for zero-copy buffers (RabitDeviceSymAlloc)
-  size_t device_oneshot_max = 512 << 10;     // bytes: <= -> one-shot kernel
+  size_t device_oneshot_max = 0;             // bytes: <= -> one-shot kernel; 0 = table by world size
   size_t device_nvls_min = 0;                // bytes: >= -> multimem kernel when available; 0 = table by world size
   size_t device_ll_max = 0;                  // bytes: <= -> tagged-word kernel; 0 = table by world size
   size_t device_stream_min = 0;              // bytes: >= -> chunked, copy-engine fed allreduce; 0 = table (128 MiB)
