@@ -436,6 +436,8 @@ def run_ours(args):
                 if per > 0:
                     put("allgather", timed(lambda: rt.allgather_async_(v[:per * n], me * per, per), it, 3, rt.synchronize),
                         (n - 1.0) / n)
+                    put("allgather_sym", timed(lambda: rt.allgather_async_(vs[:per * n], me * per, per), it, 3, rt.synchronize),
+                        (n - 1.0) / n)
             if have_nccl:
                 put("nccl_allreduce", timed_nccl(dist, torch, v, it, 3, rabit, np))
                 put("nccl_broadcast", timed_nccl(dist, torch, v, it, 3, rabit, np, kind="bcast"), 1.0)

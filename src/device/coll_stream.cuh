@@ -38,6 +38,9 @@ struct StreamArgs {
   size_t src_off;   // arena-relative start of this chunk in every rank's source region
   size_t res_off;   // arena-relative start of this chunk in every rank's result region
   int fill_result;  // P2P: also copy the tiles this rank does not own into its own result region
+  int res_in_stage; // NVLS: the result region is this op's stage (chosen by the op's parity on the device); res_off unused
+  int gate;         // NVLS: single-kernel recoverable op: nothing is written to the destinations unless the whole grid
+                    // passed its last barrier (CommitGate), so no backup of the caller's buffer is needed
 };
 
 /*! \brief store one result vector to whichever destinations exist (user may be unaligned, keep never is) */
@@ -171,8 +174,9 @@ __device__ __forceinline__ void StreamNvlsBody(const Params &p, const StreamArgs
   const size_t tile_vecs = static_cast<size_t>(blockDim.x) * kNvlsUnroll;
   const size_t ntiles = (nvec + tile_vecs - 1) / tile_vecs;
   const int n = p.world;
+  const size_t res_off = a.res_in_stage ? kCtrlBytes + static_cast<size_t>(OpEpoch(p) & 1u) * p.stage_bytes : a.res_off;
   const char *mc_src = p.mc_arena + a.src_off;
-  char *mc_res = p.mc_arena + a.res_off;
+  char *mc_res = p.mc_arena + res_off;
   for (size_t tile = blockIdx.x, k = 0; tile < ntiles; tile += gridDim.x, ++k) {
     if (TileOwner(k, n) != me) continue;
     const size_t v0 = tile * tile_vecs + threadIdx.x;
@@ -190,11 +194,12 @@ __device__ __forceinline__ void StreamNvlsBody(const Params &p, const StreamArgs
   }
   Stamp(p, 3);
   verdict = FlagBarrier(p, me, MidRow{}, OpEpoch(p) + 1, 0u, false, &s_verdict);
+  if (a.gate) verdict = CommitGate(p, me, verdict, &s_verdict);   // all blocks or none
   if (verdict != kStOk) { Report(p, me, verdict); return; }
   Stamp(p, 4);
   if (user != nullptr || keep != nullptr) {
     // every tile of this channel now sits, fully reduced, in OUR result region
-    const char *src = p.arena[me] + a.res_off;
+    const char *src = p.arena[me] + res_off;
     constexpr int kHalf = kNvlsUnroll / 2;   // keeps the register count of the whole kernel low
     for (size_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
 #pragma unroll 1
