@@ -47,20 +47,27 @@ void *RabitDeviceSymAlloc(size_t nbytes);
 void RabitDeviceSymReset(void);
 
 /* ---- tuning ------------------------------------------------------------------------------- */
-/* algo: "auto", "oneshot", "twoshot", "tma", "nvls", "pipe", "nvlspipe", "staged" (NULL keeps it);
+/* algo: "auto", "ll", "oneshot", "twoshot", "tma", "nvls", "staged", "nostream" (NULL keeps it);
  * blocks: grid cap, 0 = default; trace != 0: block 0 records %globaltimer at its phase boundaries */
 void RabitDeviceSetTuning(const char *algo, int blocks, int trace);
 void RabitDeviceGetTrace(unsigned long long *out6);
 
 /* ---- single-GPU emulation of an nranks-wide collective ----------------------------------- */
 /* kind 0 allreduce (size = elements), 1 broadcast (size = bytes), 2 allgather (size = total bytes);
- * algo 1 one-shot, 2 two-shot, 3 two-shot/TMA, 5 pipelined; bufs[r]/keeps[r] device pointers per
+ * algo 1 one-shot, 2 two-shot, 3 two-shot/TMA, 9 tagged words (<= 32 KiB); bufs[r]/keeps[r] device pointers per
  * emulated rank; codes[r] consensus words (NULL = 0); status_out[r]: 0 ok, 1 mismatch, 2 timeout.
  * Allocates its arenas with cudaMalloc on first use. Returns 0 or a negative API error. */
 int RabitEmuCollective(int kind, int algo, int nranks, void **bufs, void **keeps, size_t size, int dtype, int op,
                        int root, const size_t *slice_begin, const size_t *slice_end, const unsigned *codes,
                        int blocks, int timeout_ms, int *status_out);
 void RabitEmuReset(void);
+/* The chunked (streamed) allreduce on emulated ranks: chunks of chunk_bytes are copied into each rank's stage and
+ * reduced by one StreamP2P launch each; fail_chunk >= 0 injects a consensus mismatch there, after which the call
+ * restores bufs[r] from the stage copy like the multi-GPU path does. status_out[r]: first failure of rank r. */
+int RabitEmuStreamAllreduce(int nranks, void **bufs, void **keeps, size_t count, int dtype, int op, size_t chunk_bytes,
+                            int fail_chunk, int blocks, int *status_out);
+/* Test hook: set the op counter of the emulated ranks (flag rows made consistent with it). */
+int RabitEmuSetEpoch(int nranks, size_t payload_bytes, unsigned int epoch);
 
 /* ---- allocation-free variant -------------------------------------------------------------- */
 /* No counterpart in the reference. The emulated two-shot allreduce for callers that must not trigger

@@ -101,6 +101,7 @@ def launch(cmd, nworker, max_attempts=20, env=None, capture=False, timeout=None,
     procs = {}
 
     use_standby = standby and placement is None
+    ended = {}
     fifo_dir = tempfile.mkdtemp(prefix="rabit-standby-") if use_standby else None
     fifo_count = [0]
 
@@ -196,17 +197,28 @@ def launch(cmd, nworker, max_attempts=20, env=None, capture=False, timeout=None,
         attempt = 0
         chunks = []
         spare = first_spares.get(i)
+        next_spare_at = 0.0
         p = None
         while True:
             if p is None:
                 p = start(i, attempt)
-            if use_standby and spare is None:
+            if use_standby and spare is None and time.time() >= next_spare_at:
                 spare = start_standby(i)
             with lock:
                 procs[i] = p
             try:
                 remaining = None if deadline is None else max(deadline - time.time(), 0.1)
-                out, _ = p.communicate(timeout=remaining)
+                if use_standby and spare is None:
+                    # the next standby is started a little later: its start-up (CUDA context creation contends for
+                    # the driver) must not slow down the recovery that is going on right now
+                    try:
+                        out, _ = p.communicate(timeout=min(max(next_spare_at - time.time(), 0.05), remaining or 1e9))
+                    except subprocess.TimeoutExpired:
+                        if deadline is not None and time.time() >= deadline:
+                            raise
+                        continue
+                else:
+                    out, _ = p.communicate(timeout=remaining)
             except subprocess.TimeoutExpired:
                 p.kill()
                 out, _ = p.communicate()
@@ -231,6 +243,9 @@ def launch(cmd, nworker, max_attempts=20, env=None, capture=False, timeout=None,
                 else:
                     discard(spare)
                 spare = None
+                next_spare_at = time.time() + 1.5
+        with lock:
+            ended[i] = time.time()
         if spare is not None:
             discard(spare)
         with lock:
@@ -244,7 +259,7 @@ def launch(cmd, nworker, max_attempts=20, env=None, capture=False, timeout=None,
         t.start()
     for t in threads:
         t.join()
-    res.wall = time.time() - t0
+    res.wall = (max(ended.values()) if ended else time.time()) - t0   # (without the clean-up of unused standbys)
     if fifo_dir is not None:
         try:
             os.rmdir(fifo_dir)
