@@ -115,7 +115,22 @@ class ClockSampler(object):
 
 
 def nvlink_bytes(gpu):
-    """Cumulative NVLink (rx, tx) KiB of one GPU from nvidia-smi, or None if the counters are not exposed."""
+    """Cumulative NVLink (rx, tx) KiB of one GPU, summed over its links: NVML field values first, the nvidia-smi
+    table as a fallback; None if the counters are not exposed."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(gpu)
+        vals = pynvml.nvmlDeviceGetFieldValues(h, [(pynvml.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_RX, 0xFFFFFFFF),
+                                                   (pynvml.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_TX, 0xFFFFFFFF)])
+        out = []
+        for v in vals:
+            if v.nvmlReturn != 0:
+                raise RuntimeError("field not available")
+            out.append(int(v.value.ullVal))
+        return tuple(out)
+    except Exception:  # pylint: disable=broad-except
+        pass
     try:
         r = subprocess.run(["nvidia-smi", "nvlink", "-gt", "d", "-i", str(gpu)], stdout=subprocess.PIPE,
                            stderr=subprocess.DEVNULL, timeout=20)
