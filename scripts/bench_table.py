@@ -40,9 +40,11 @@ def main():
         print("## N = %d\n" % n)
         print("`%s`\n" % d["config"]["backend"])
         rs, asym, apl, nc = d.get("robust_symmetric"), d.get("async_symmetric"), d.get("async_plain"), d.get("nccl")
-        print("* headline 256 MiB f32 Sum, **robust API, ordinary tensor: %s us** (busbw %s GB/s = %s of 900, %s of the measured 770)"
-              % (f(d["ms_per_step"] * 1e3), f(d["busbw_GBps"]), f(d.get("nvlink_roofline_frac"), 2), f(d.get("busbw_frac_of_770_measured"), 2)))
-        print("  - robust API, symmetric tensor: %s us; async plain: %s us; async symmetric: %s us (busbw %s = %s of 900); NCCL: %s us (busbw %s)"
+        print("* headline 256 MiB f32 Sum, **robust API, ordinary tensor: %s us** (busbw %s GB/s = %s of 900, %s of the "
+              "measured 770)" % (f(d["ms_per_step"] * 1e3), f(d["busbw_GBps"]), f(d.get("nvlink_roofline_frac"), 2),
+                                 f(d.get("busbw_frac_of_770_measured"), 2)))
+        print("  - robust API, symmetric tensor: %s us; async plain: %s us; async symmetric: %s us (busbw %s = %s of 900); "
+              "NCCL: %s us (busbw %s)"
               % (f(rs and rs["ms_per_step"] * 1e3), f(apl and apl["ms_per_step"] * 1e3), f(asym and asym["ms_per_step"] * 1e3),
                  f(asym and asym["busbw_GBps"]), f(asym and asym.get("busbw_frac_of_900"), 2), f(nc and nc["ms_per_step"] * 1e3),
                  f(nc and nc["busbw_GBps"])))
@@ -52,7 +54,8 @@ def main():
               " (%s GB/s aggregate); the caller doing the two copies around the device call: %s ms; copy ceiling of this box at this N"
               " (all ranks H2D + D2H at once, no collective): %s ms%s"
               % (f(e["ms_per_step"], 2), f(e["value"]), f(e["manual_copy_ms_per_step"], 2), f(e["copy_ceiling_ms"], 2),
-                 ("; reference (host TCP engine): %s ms/step -> **%sx**" % (f(r["ms_per_step"], 0), f(r["ms_per_step"] / e["ms_per_step"]))) if r else ""))
+                 ("; reference (host TCP engine): %s ms/step -> **%sx**"
+                  % (f(r["ms_per_step"], 0), f(r["ms_per_step"] / e["ms_per_step"]))) if r else ""))
         rec = d.get("recovery") or {}
         cold = rec.get("without_standby_workers") or {}
         rr = (r or {}).get("recovery") or {}
@@ -69,7 +72,8 @@ def main():
                   % (f(h.get("sym_us")), f(h.get("staged_us")), f(h.get("nccl_us")), f(h.get("robust_api_us"))))
         sw = d.get("sweep") or []
         if sw:
-            print("\n| bytes | allreduce robust us | async plain | async sym | graph | NCCL | broadcast plain | sym | NCCL | allgather plain | sym | NCCL |")
+            print("\n| bytes | allreduce robust us | async plain | async sym | graph | NCCL | broadcast plain | sym | NCCL "
+                  "| allgather plain | sym | NCCL |")
             print("|---:|---:|---:|---:|---:|---:|---:|---:|---:|---:|---:|---:|")
             for row in sw:
                 g = lambda k: f(row.get(k))  # noqa: E731
