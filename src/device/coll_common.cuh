@@ -89,6 +89,7 @@ struct Params {
   int device_epoch;           // 1: take the op epoch from Control::epoch_dev instead of `epoch` (graph-replayable)
   int chained;                // index of this kernel inside a multi-kernel op (0 = first, or a single-kernel op):
                               // a later kernel leaves at once if an earlier one of the same op failed
+  unsigned int block_base;    // first flag row of this kernel (chunk kernels of one op that run concurrently)
 };
 
 /*! \brief the op epoch of the running kernel. With device_epoch it was fetched from the control block by BeginOp

@@ -24,8 +24,9 @@ namespace rabit {
 namespace device {
 
 struct ExitRow {
+  unsigned int base = 0;
   __device__ __forceinline__ unsigned long long *operator()(Control *c) const {
-    return &c->exit_[blockIdx.x][0];
+    return &c->exit_[blockIdx.x + base][0];
   }
 };
 

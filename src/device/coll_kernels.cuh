@@ -26,15 +26,19 @@
 namespace rabit {
 namespace device {
 
+// `base` shifts a kernel onto its own set of flag rows: two chunk kernels of one streamed op that run at the same
+// time (device_backend_stream.inc, "lanes") must not share rows
 struct EntryRow {
   unsigned int par;
+  unsigned int base = 0;
   __device__ __forceinline__ unsigned long long *operator()(Control *c) const {
-    return &c->entry[par][blockIdx.x][0];
+    return &c->entry[par][blockIdx.x + base][0];
   }
 };
 struct MidRow {
+  unsigned int base = 0;
   __device__ __forceinline__ unsigned long long *operator()(Control *c) const {
-    return &c->mid[blockIdx.x][0];
+    return &c->mid[blockIdx.x + base][0];
   }
 };
 

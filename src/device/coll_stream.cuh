@@ -75,7 +75,7 @@ __device__ __forceinline__ void StreamP2PBody(const Params &p, const StreamArgs 
   char *keep = static_cast<char *>(p.keep[ix]);
   const bool aligned = (reinterpret_cast<uintptr_t>(user) % kVec) == 0;
   Stamp(p, 0);
-  int verdict = FlagBarrier(p, me, EntryRow{OpEpoch(p) & 1u}, OpEpoch(p) + 1, p.code[ix], true, &s_verdict, false);
+  int verdict = FlagBarrier(p, me, EntryRow{OpEpoch(p) & 1u, p.block_base}, OpEpoch(p) + 1, p.code[ix], true, &s_verdict, false);
   if (verdict != kStOk) { Report(p, me, verdict); return; }
   Stamp(p, 2);
   const size_t nvec_full = p.bytes / kVec;
@@ -119,7 +119,7 @@ __device__ __forceinline__ void StreamP2PBody(const Params &p, const StreamArgs 
     }
   }
   Stamp(p, 3);
-  verdict = FlagBarrier(p, me, MidRow{}, OpEpoch(p) + 1, 0u, false, &s_verdict);
+  verdict = FlagBarrier(p, me, MidRow{p.block_base}, OpEpoch(p) + 1, 0u, false, &s_verdict);
   if (verdict != kStOk) { Report(p, me, verdict); return; }
   Stamp(p, 4);
   // allgather: pull every tile this rank does not own from its owner's result region
@@ -144,7 +144,7 @@ __device__ __forceinline__ void StreamP2PBody(const Params &p, const StreamArgs 
     }
   }
   // a peer may still be pulling from OUR result region: nobody leaves (and lets the next op write into it) early
-  verdict = FlagBarrier(p, me, ExitRow{}, OpEpoch(p) + 1, 0u, false, &s_verdict, false);
+  verdict = FlagBarrier(p, me, ExitRow{p.block_base}, OpEpoch(p) + 1, 0u, false, &s_verdict, false);
   if (verdict != kStOk) { Report(p, me, verdict); return; }
   Stamp(p, 5);
 }
@@ -166,7 +166,7 @@ __device__ __forceinline__ void StreamNvlsBody(const Params &p, const StreamArgs
   char *keep = static_cast<char *>(p.keep[0]);
   const bool aligned = (reinterpret_cast<uintptr_t>(user) % kVec) == 0;
   Stamp(p, 0);
-  int verdict = FlagBarrier(p, me, EntryRow{OpEpoch(p) & 1u}, OpEpoch(p) + 1, p.code[0], true, &s_verdict, false);
+  int verdict = FlagBarrier(p, me, EntryRow{OpEpoch(p) & 1u, p.block_base}, OpEpoch(p) + 1, p.code[0], true, &s_verdict, false);
   if (verdict != kStOk) { Report(p, me, verdict); return; }
   Stamp(p, 2);
   const size_t nvec_full = p.bytes / kVec;
@@ -193,7 +193,7 @@ __device__ __forceinline__ void StreamNvlsBody(const Params &p, const StreamArgs
     }
   }
   Stamp(p, 3);
-  verdict = FlagBarrier(p, me, MidRow{}, OpEpoch(p) + 1, 0u, false, &s_verdict);
+  verdict = FlagBarrier(p, me, MidRow{p.block_base}, OpEpoch(p) + 1, 0u, false, &s_verdict);
   if (a.gate) verdict = CommitGate(p, me, verdict, &s_verdict);   // all blocks or none
   if (verdict != kStOk) { Report(p, me, verdict); return; }
   Stamp(p, 4);
