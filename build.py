@@ -133,6 +133,8 @@ def build(cuda=True, verbose=False, programs=True):
 
     with open(flavour, "w") as fo:
         fo.write(want)
+    if cuda:
+        build_torch_extension(verbose)
     if programs:
         bin_dir = os.path.join(ROOT, "build", "bin")
         os.makedirs(bin_dir, exist_ok=True)
@@ -156,6 +158,35 @@ def build(cuda=True, verbose=False, programs=True):
         with concurrent.futures.ThreadPoolExecutor(max_workers=os.cpu_count() or 4) as ex:
             for f in [ex.submit(run, c, not verbose) for c in pjobs]:
                 f.result()
+    return True
+
+
+def build_torch_extension(verbose=False):
+    """rabit_b200/_torch_ext*.so: the pybind11 / libtorch binding (src/python/torch_ext.cc). Host C++ only; it does not
+    link the engine library (symbols are resolved from whichever lib/librabit*.so rabit.py loaded). Skipped with a note
+    when torch is not importable: torch_binding.py then stays on its ctypes path."""
+    try:
+        import sysconfig
+        import torch  # noqa: F401
+        from torch.utils import cpp_extension as ce
+        import pybind11
+    except Exception as e:  # pylint: disable=broad-except
+        print("torch extension skipped: %s" % e)
+        return False
+    src = os.path.join(ROOT, "src", "python", "torch_ext.cc")
+    target = os.path.join(ROOT, "rabit_b200", "_torch_ext" + sysconfig.get_config_var("EXT_SUFFIX"))
+    if not newer([src], target):
+        return True
+    import torch
+    incs = ce.include_paths() + [pybind11.get_include(), sysconfig.get_paths()["include"],
+                                 os.path.join(os.path.dirname(os.path.dirname(find_nvcc())), "include")]
+    libdirs = ce.library_paths()
+    cmd = (["g++", "-std=c++17", "-O2", "-fPIC", "-shared", "-Wall", "-Wno-unused-function",
+            "-DTORCH_EXTENSION_NAME=_torch_ext", "-DTORCH_API_INCLUDE_EXTENSION_H",
+            "-D_GLIBCXX_USE_CXX11_ABI=%d" % int(torch._C._GLIBCXX_USE_CXX11_ABI)] +
+           ["-I" + i for i in incs] + [src, "-o", target] + ["-L" + d for d in libdirs] +
+           ["-Wl,-rpath," + d for d in libdirs] + ["-ltorch_python", "-ltorch", "-ltorch_cpu", "-lc10", "-lc10_cuda", "-ldl"])
+    run(cmd, not verbose)
     return True
 
 

@@ -10,10 +10,25 @@ No counterpart in the reference (it predates GPU tensors); the semantics of each
 those of ``rabit::Allreduce/Broadcast/Allgather`` (reference include/rabit/rabit.h).
 """
 import ctypes
+import os
 
 import torch
 
 from . import rabit as _rabit
+
+# The native binding (src/python/torch_ext.cc, built by build.py as rabit_b200/_torch_ext*.so): same calls without
+# the per-call ctypes / Python work (~4-5 us each). RABIT_TORCH_CTYPES=1 forces the ctypes path below.
+try:
+    if os.environ.get("RABIT_TORCH_CTYPES"):
+        raise ImportError("disabled")
+    from . import _torch_ext as _ext
+except ImportError:
+    _ext = None
+
+
+def native_binding():
+    """True when the pybind11 / libtorch extension carries the tensor calls (False: ctypes fallback)."""
+    return _ext is not None
 
 _TORCH_DTYPE = {
     torch.int8: 0, torch.uint8: 1, torch.int32: 2, torch.int64: 4,
@@ -77,6 +92,8 @@ def describe():
 
 def _reset_stream_cache():
     _last_stream[0] = None
+    if _ext is not None:
+        _ext.reset_stream_cache()
 
 
 def device_active():
@@ -93,6 +110,8 @@ def allreduce_(tensor, op=_rabit.SUM, prepare_fun=None):
     ``tensor`` on this rank (rabit semantics)."""
     lib = _lib()
     _check(tensor)
+    if _ext is not None and prepare_fun is None:
+        return _ext.allreduce_(tensor, op)
     keep = None
     fptr = None
     if prepare_fun is not None:
@@ -114,6 +133,8 @@ def broadcast_(tensor, root=0):
     """Fault-tolerant in-place broadcast of the tensor's bytes from ``root``."""
     lib = _lib()
     _check(tensor)
+    if _ext is not None:
+        return _ext.broadcast_(tensor, root)
     if tensor.is_cuda:
         _bind_stream(lib, tensor)
     lib.RabitBroadcast(ctypes.c_void_p(tensor.data_ptr()), tensor.numel() * tensor.element_size(), root)
@@ -134,6 +155,8 @@ def allgather_(out, begin, count, prev_count=None):
 
 def allreduce_async_(tensor, op=_rabit.SUM):
     """Enqueue an in-place allreduce on the current CUDA stream and return immediately."""
+    if _ext is not None:
+        return _ext.allreduce_async_(tensor, op)
     lib = _lib()
     _check(tensor)
     if not tensor.is_cuda:
@@ -146,6 +169,8 @@ def allreduce_async_(tensor, op=_rabit.SUM):
 
 
 def broadcast_async_(tensor, root=0):
+    if _ext is not None:
+        return _ext.broadcast_async_(tensor, root)
     lib = _lib()
     _check(tensor)
     _bind_stream(lib, tensor)
@@ -158,6 +183,8 @@ def broadcast_async_(tensor, root=0):
 def allgather_async_(out, begin, count):
     """Enqueue a ring-ordered allgather on the current CUDA stream: this rank owns
     ``out.view(-1)[begin:begin+count]``, every other range is filled in from its owner."""
+    if _ext is not None:
+        return _ext.allgather_async_(out, begin, count)
     lib = _lib()
     _check(out)
     if not out.is_cuda:
@@ -172,6 +199,8 @@ def allgather_async_(out, begin, count):
 
 def synchronize():
     """Wait for the enqueued collectives; raises if a peer was lost or timed out."""
+    if _ext is not None:
+        return _ext.synchronize()
     rc = _lib().RabitDeviceSynchronize()
     if rc != 0:
         raise RuntimeError("device collective failed: %s" %

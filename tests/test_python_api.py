@@ -87,3 +87,32 @@ def test_lib_mpi_selects_the_library_backed_engine():
     env = dict(os.environ, PYTHONPATH=ROOT)
     r = subprocess.run([sys.executable, "-c", code], env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, timeout=120)
     assert r.returncode == 0 and b"mpi-lib-ok" in r.stdout, r.stdout.decode()
+
+
+def test_native_torch_binding_on_cpu_tensors():
+    """the pybind11 / libtorch extension (src/python/torch_ext.cc) carries the tensor calls; CPU tensors go through the
+    host engine, also across a scripted kill (world 3), and the ctypes fallback gives the same answers"""
+    code = ("import sys, os\nimport torch\nfrom rabit_b200 import rabit, torch_binding as rt\n"
+            "want_native = os.environ.get('RABIT_TORCH_CTYPES') is None\n"
+            "assert rt.native_binding() == want_native, rt.native_binding()\n"
+            "rabit.init(sys.argv, lib='mock')\n"
+            "me, n = rabit.get_rank(), rabit.get_world_size()\n"
+            "v, m = rabit.load_checkpoint()\n"
+            "for it in range(v, 3):\n"
+            "    t = torch.arange(1000, dtype=torch.float64) * (me + 1) + it\n"
+            "    rt.allreduce_(t)\n"
+            "    assert torch.equal(t, torch.arange(1000, dtype=torch.float64) * (n * (n + 1) // 2) + it * n)\n"
+            "    b = torch.full((77,), me, dtype=torch.int32)\n"
+            "    rt.broadcast_(b, it % n)\n"
+            "    assert torch.equal(b, torch.full((77,), it % n, dtype=torch.int32))\n"
+            "    rabit.checkpoint(it)\n"
+            "rabit.tracker_print('[%d] torch binding ok\\n' % me)\n"
+            "rabit.finalize()\n")
+    env = {"PYTHONPATH": ROOT + os.pathsep + os.environ.get("PYTHONPATH", "")}
+    for extra in ({}, {"RABIT_TORCH_CTYPES": "1"}):
+        e = dict(env)
+        e.update(extra)
+        res = run_job([sys.executable, "-c", code, "mock=1,1,1,0"], 3, timeout=180, env=e)
+        assert res.ok, res.outputs
+        assert res.restarts == 1
+        assert sum("torch binding ok" in m for m in res.messages) == 3
