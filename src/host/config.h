@@ -62,7 +62,8 @@ struct Config {
   size_t device_oneshot_max = 0;             // bytes: <= -> one-shot kernel; 0 = table by world size
   size_t device_nvls_min = 0;                // bytes: >= -> multimem kernel when available; 0 = table by world size
   size_t device_ll_max = 0;                  // bytes: <= -> tagged-word kernel; 0 = table by world size
-  size_t device_stream_min = 0;              // bytes: >= -> chunked, copy-engine fed allreduce; 0 = table (128 MiB)
+  size_t device_stream_min = 0;              // bytes: >= -> chunked, copy-engine fed allreduce of DEVICE buffers; 0 = table
+                                             // (128 MiB with 2 ranks, off otherwise), 1 = off
   size_t device_stream_chunk = 0;            // bytes per chunk of that path; 0 = table (512 MiB)
   size_t device_stream_first = 0;            // bytes of its first chunk; 0 = table (64 MiB)
   std::string device_tune = "";              // file with measured thresholds (benchmarks/algo_sweep.py --emit-table)
