@@ -81,7 +81,7 @@ def ssh_command(ssh, host, cwd, env, cmd):
 
 def launch(cmd, nworker, max_attempts=20, env=None, capture=False, timeout=None,
            per_rank_gpu=False, verbose=False, host="127.0.0.1", hosts=None, ssh=("ssh", "-o", "StrictHostKeyChecking=no"),
-           standby=False):
+           standby=False, standby_respawn_s=10.0):
     """Run ``cmd`` (argv list) as ``nworker`` processes under a fresh tracker.
 
     per_rank_gpu: export RABIT_DEVICE_ORDINAL / RABIT_LOCAL_RANK so a task uses the GPU with its index on its host.
@@ -90,8 +90,9 @@ def launch(cmd, nworker, max_attempts=20, env=None, capture=False, timeout=None,
     standby: keep one pre-started process per task (local workers only): it runs the program up to ``rabit::Init``,
       where the engine creates the CUDA context and then sleeps on a fifo (``RABIT_STANDBY_FIFO``). When the live
       worker of the task dies, the standby is handed its life (one line with the attempt number) instead of a new
-      process being started, and a fresh standby is started behind it. Recover-after-kill then no longer contains
-      process start-up, library loading and CUDA context creation.
+      process being started, and a fresh standby is started behind it ``standby_respawn_s`` seconds later (creating a
+      CUDA context stalls the other processes on that GPU for a moment: not while the job is still catching up).
+      Recover-after-kill then no longer contains process start-up, library loading and CUDA context creation.
     """
     placement = place_tasks(hosts, nworker) if hosts else None
     tracker = Tracker(nworker, host=host, verbose=verbose).start()
@@ -243,7 +244,7 @@ def launch(cmd, nworker, max_attempts=20, env=None, capture=False, timeout=None,
                 else:
                     discard(spare)
                 spare = None
-                next_spare_at = time.time() + 1.5
+                next_spare_at = time.time() + standby_respawn_s
         with lock:
             ended[i] = time.time()
         if spare is not None:
