@@ -26,6 +26,9 @@ except ImportError:
     _ext = None
 
 
+_bound = [None]     # the ctypes library whose entry points the native module currently calls
+
+
 def native_binding():
     """True when the pybind11 / libtorch extension carries the tensor calls (False: ctypes fallback)."""
     return _ext is not None
@@ -50,6 +53,12 @@ def _lib():
         lib.RabitDeviceLaunchCount.restype = c.c_ulonglong
         lib.RabitDeviceDescribe.argtypes = [c.c_char_p, c.c_size_t]
         lib._rabit_device_declared = True
+    if _ext is not None and _bound[0] is not lib:
+        # hand the native module the entry points of THIS library (a process may hold several librabit*.so)
+        names = ["RabitDeviceAllreduceAsync", "RabitDeviceBroadcastAsync", "RabitDeviceAllgatherAsync", "RabitDeviceSynchronize",
+                 "RabitDeviceSetStream", "RabitAllreduce", "RabitBroadcast", "RabitDeviceLaunchCount"]
+        _ext.bind_library(dict((n, ctypes.cast(getattr(lib, n), ctypes.c_void_p).value) for n in names))
+        _bound[0] = lib
     return lib
 
 
@@ -94,6 +103,8 @@ def _reset_stream_cache():
     _last_stream[0] = None
     if _ext is not None:
         _ext.reset_stream_cache()
+        _ext.unbind_library()
+        _bound[0] = None
 
 
 def device_active():
@@ -155,9 +166,9 @@ def allgather_(out, begin, count, prev_count=None):
 
 def allreduce_async_(tensor, op=_rabit.SUM):
     """Enqueue an in-place allreduce on the current CUDA stream and return immediately."""
+    lib = _lib()
     if _ext is not None:
         return _ext.allreduce_async_(tensor, op)
-    lib = _lib()
     _check(tensor)
     if not tensor.is_cuda:
         raise ValueError("allreduce_async_ needs a CUDA tensor")
@@ -169,9 +180,9 @@ def allreduce_async_(tensor, op=_rabit.SUM):
 
 
 def broadcast_async_(tensor, root=0):
+    lib = _lib()
     if _ext is not None:
         return _ext.broadcast_async_(tensor, root)
-    lib = _lib()
     _check(tensor)
     _bind_stream(lib, tensor)
     rc = lib.RabitDeviceBroadcastAsync(ctypes.c_void_p(tensor.data_ptr()), tensor.numel() * tensor.element_size(), root)
@@ -183,9 +194,9 @@ def broadcast_async_(tensor, root=0):
 def allgather_async_(out, begin, count):
     """Enqueue a ring-ordered allgather on the current CUDA stream: this rank owns
     ``out.view(-1)[begin:begin+count]``, every other range is filled in from its owner."""
+    lib = _lib()
     if _ext is not None:
         return _ext.allgather_async_(out, begin, count)
-    lib = _lib()
     _check(out)
     if not out.is_cuda:
         raise ValueError("allgather_async_ needs a CUDA tensor")
@@ -199,9 +210,10 @@ def allgather_async_(out, begin, count):
 
 def synchronize():
     """Wait for the enqueued collectives; raises if a peer was lost or timed out."""
+    lib = _lib()
     if _ext is not None:
         return _ext.synchronize()
-    rc = _lib().RabitDeviceSynchronize()
+    rc = lib.RabitDeviceSynchronize()
     if rc != 0:
         raise RuntimeError("device collective failed: %s" %
                            {1: "consensus mismatch", 2: "peer timeout", 3: "peer lost"}.get(rc, rc))

@@ -4,14 +4,13 @@
  * The ctypes binding pays ~4-5 us of interpreter work per call (argument marshalling, stream lookup through
  * Python), which is half the cost of a small stream-ordered collective. Here a call is: read the tensor's
  * pointer / size / dtype, take torch's current CUDA stream, call the C entry point. The engine library is NOT
- * linked: rabit_b200.rabit loads one of lib/librabit*.so with RTLD_GLOBAL (which one decides the engine), and
- * this module resolves the C symbols from the global namespace on first use, so both bindings drive the same
- * engine instance. No counterpart in the reference (its python module is ctypes only, python/rabit.py).
+ * linked: rabit_b200.rabit loads one of lib/librabit*.so (which one decides the engine) and torch_binding hands
+ * this module the addresses of that library's C entry points, so both bindings drive the same engine instance. No counterpart in the reference (its python module is ctypes only, python/rabit.py).
  */
 #include <ATen/cuda/CUDAContext.h>
-#include <dlfcn.h>
 #include <torch/extension.h>
 
+#include <cstdint>
 #include <stdexcept>
 #include <string>
 
@@ -29,28 +28,36 @@ struct Api {
   bool ok = false;
 };
 
+Api g_api;
+
 template <typename F>
-void Bind(const char *name, F *fn) {
-  void *p = dlsym(RTLD_DEFAULT, name);
-  if (p == nullptr) throw std::runtime_error(std::string("rabit engine library is not loaded (") + name +
-                                             " not found): call rabit_b200.rabit.init() first");
-  *fn = reinterpret_cast<F>(p);
+void Take(const pybind11::dict &addr, const char *name, F *fn) {
+  if (!addr.contains(name)) throw std::runtime_error(std::string("rabit torch extension: no address for ") + name);
+  *fn = reinterpret_cast<F>(static_cast<uintptr_t>(addr[name].cast<unsigned long long>()));  // NOLINT(*)
+}
+
+/*!
+ * \brief called by torch_binding with the addresses of the C entry points of the library that rabit.py loaded
+ *  (taken through ctypes from that very handle): a process may hold several lib/librabit*.so, and a lookup in
+ *  the global namespace would silently pick the first one.
+ */
+void BindLibrary(const pybind11::dict &addr) {
+  Api api;
+  Take(addr, "RabitDeviceAllreduceAsync", &api.allreduce_async);
+  Take(addr, "RabitDeviceBroadcastAsync", &api.broadcast_async);
+  Take(addr, "RabitDeviceAllgatherAsync", &api.allgather_async);
+  Take(addr, "RabitDeviceSynchronize", &api.synchronize);
+  Take(addr, "RabitDeviceSetStream", &api.set_stream);
+  Take(addr, "RabitAllreduce", &api.allreduce);
+  Take(addr, "RabitBroadcast", &api.broadcast);
+  Take(addr, "RabitDeviceLaunchCount", &api.launch_count);
+  api.ok = true;
+  g_api = api;
 }
 
 Api &GetApi() {
-  static Api api;
-  if (!api.ok) {
-    Bind("RabitDeviceAllreduceAsync", &api.allreduce_async);
-    Bind("RabitDeviceBroadcastAsync", &api.broadcast_async);
-    Bind("RabitDeviceAllgatherAsync", &api.allgather_async);
-    Bind("RabitDeviceSynchronize", &api.synchronize);
-    Bind("RabitDeviceSetStream", &api.set_stream);
-    Bind("RabitAllreduce", &api.allreduce);
-    Bind("RabitBroadcast", &api.broadcast);
-    Bind("RabitDeviceLaunchCount", &api.launch_count);
-    api.ok = true;
-  }
-  return api;
+  if (!g_api.ok) throw std::runtime_error("rabit engine library is not bound: call rabit_b200.rabit.init() first");
+  return g_api;
 }
 
 /*! \brief torch dtype -> rabit::engine::mpi::DataType */
@@ -163,4 +170,6 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
   m.def("synchronize", &Synchronize, "wait for the enqueued collectives");
   m.def("launch_count", []() { return GetApi().launch_count(); });
   m.def("reset_stream_cache", &ResetStreamCache);
+  m.def("bind_library", &BindLibrary, "addresses of the engine's C entry points (from the ctypes handle in use)");
+  m.def("unbind_library", []() { g_api = Api(); });
 }
