@@ -5,7 +5,8 @@
  * Python), which is half the cost of a small stream-ordered collective. Here a call is: read the tensor's
  * pointer / size / dtype, take torch's current CUDA stream, call the C entry point. The engine library is NOT
  * linked: rabit_b200.rabit loads one of lib/librabit*.so (which one decides the engine) and torch_binding hands
- * this module the addresses of that library's C entry points, so both bindings drive the same engine instance. No counterpart in the reference (its python module is ctypes only, python/rabit.py).
+ * this module the addresses of that library's C entry points, so both bindings drive the same engine instance.
+ * No counterpart in the reference (its python module is ctypes only, python/rabit.py).
  */
 #include <ATen/cuda/CUDAContext.h>
 #include <torch/extension.h>
