@@ -29,7 +29,7 @@ import sys
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 HOST_SRCS = ["comm", "engine_base", "engine_robust", "engine_recover", "engine_ops",
-             "engine_mock", "result_store", "c_api"]
+             "engine_mock", "result_store", "c_api", "fake_device"]
 ENGINES = {"librabit.so": "robust", "librabit_mock.so": "mock",
            "librabit_base.so": "base", "librabit_empty.so": "empty", "librabit_nccl.so": "nccl"}
 CXXFLAGS = ["-std=c++17", "-O3", "-g", "-Wall", "-fPIC", "-pthread", "-I" + os.path.join(ROOT, "include")]

@@ -17,7 +17,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 from rabit_b200.parallel.launcher import launch  # noqa: E402
 
-HOST = ["comm", "engine_base", "engine_robust", "engine_recover", "engine_ops", "engine_mock", "result_store",
+HOST = ["comm", "engine_base", "engine_robust", "engine_recover", "engine_ops", "engine_mock", "result_store", "fake_device",
         "c_api", "engine"]
 PROGRAMS = ["model_recover", "local_recover", "lazy_recover", "speed_test", "unit_tests"]
 
@@ -63,6 +63,14 @@ def main():
         ("local_recover", ["10000", "mock=0,0,1,0", "mock=1,1,1,0", "mock=0,1,1,1", "mock=4,1,1,0", "mock=5,1,1,0"], 6),
         ("lazy_recover", ["10000", "mock=0,0,1,0", "mock=1,1,1,0", "mock=1,1,1,1", "mock=0,1,1,0", "mock=4,1,1,0"], 6),
         ("model_recover", ["2000", "mock=1,1,1,0", "rabit_timeout=1", "rabit_timeout_sec=60"], 4),
+        # the device-backend side of the engines (result cache in backend memory, op pieces, backend transport for
+        # recovery payloads and local replicas) on the host-memory stand-in of the backend
+        ("model_recover", ["20000", "mock=0,0,1,0", "mock=1,1,1,0", "mock=1,1,1,1", "rabit_bootstrap_cache=1", "rabit_device=fake",
+                           "rabit_device_host_min=1", "rabit_device_blob_min=1", "rabit_device_arena=64K"], 4),
+        ("local_recover", ["20000", "mock=0,1,1,0", "mock=3,2,1,0", "rabit_device=fake", "rabit_device_host_min=1",
+                           "rabit_device_blob_min=1"], 5),
+        ("lazy_recover", ["20000", "mock=1,1,0,0", "mock=2,2,3,0", "rabit_device=fake", "rabit_device_host_min=1",
+                          "rabit_device_blob_min=1"], 4),
     ]
     bad = 0
     for prog, args, n in scenarios:

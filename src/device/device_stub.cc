@@ -6,7 +6,8 @@
 
 namespace rabit {
 namespace engine {
-DeviceBackend *DeviceBackend::Create(const Config &) { return nullptr; }
+DeviceBackend *CreateFakeBackend(const Config &cfg);  // src/host/fake_device.cc
+DeviceBackend *DeviceBackend::Create(const Config &cfg) { return cfg.device == "fake" ? CreateFakeBackend(cfg) : nullptr; }
 bool DeviceBackend::IsDevicePointer(const void *) { return false; }
 bool DeviceBackend::Compiled() { return false; }
 void DeviceBackend::RawCopy(void *, const void *, size_t, bool) {}
