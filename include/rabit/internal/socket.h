@@ -214,6 +214,9 @@ class PollHelper {
   void WatchRead(int fd) { Slot(fd).events |= POLLIN; }
   void WatchWrite(int fd) { Slot(fd).events |= POLLOUT; }
   void WatchException(int fd) { Slot(fd).events |= POLLPRI; }
+  /*! \brief wake up when the peer closes its end (no effect on what CheckRead reports for a socket not watched for reading) */
+  void WatchHangup(int fd) { Slot(fd).events |= POLLRDHUP; }
+  bool CheckHangup(int fd) const { return Revents(fd) & (POLLRDHUP | POLLHUP | POLLERR); }
   bool CheckRead(int fd) const { return Revents(fd) & (POLLIN | POLLHUP | POLLERR); }
   bool CheckWrite(int fd) const { return Revents(fd) & POLLOUT; }
   bool CheckExcept(int fd) const { return Revents(fd) & POLLPRI; }

@@ -101,6 +101,25 @@ bool HostComm::LinksBroken() {
   return false;
 }
 
+bool HostComm::WaitLinks(utils::PollHelper *poll) {
+  for (Link &l : links_) if (!l.hup_seen && !l.sock.IsClosed()) poll->WatchHangup(l.sock.fd);
+  // nothing moved for a while: a peer can also vanish without a FIN reaching us (host down), so look at every link
+  if (poll->Poll(kProbeMs) == 0) return !LinksBroken();
+  for (Link &l : links_) {
+    if (l.hup_seen || l.sock.IsClosed() || !poll->CheckHangup(l.sock.fd)) continue;
+    char c;
+    const ssize_t n = recv(l.sock.fd, &c, 1, MSG_PEEK | MSG_DONTWAIT);
+    if (n == 0 || (n < 0 && !WouldBlock())) {
+      snprintf(g_last_sock_what, sizeof(g_last_sock_what), "hang-up of %d", l.rank);
+      return false;
+    }
+    // closed behind unread bytes (payload of this op, or the bye of a peer that is done): whoever reads the
+    // link finds out; do not wake up for it again
+    l.hup_seen = true;
+  }
+  return true;
+}
+
 Link *HostComm::FindLink(int r) {
   for (Link &l : links_) if (l.rank == r) return &l;
   return nullptr;
@@ -196,7 +215,7 @@ bool HostComm::Connect(const char *cmd) {
         dialled.push_back(peer_rank);
         nl.rank = peer_rank;
         Link *old = FindLink(peer_rank);
-        if (old != nullptr) { old->sock.Close(); old->sock = nl.sock; } else { links_.push_back(nl); }
+        if (old != nullptr) { old->sock.Close(); old->sock = nl.sock; old->hup_seen = false; } else { links_.push_back(nl); }
       }
       utils::Check(t.SendInt(nerr), "tracker: send failed");
     } while (nerr != 0);
@@ -233,7 +252,7 @@ bool HostComm::Connect(const char *cmd) {
                          std::find(accepted.begin(), accepted.end(), nl.rank) != accepted.end();
       if (!known) accepted.push_back(nl.rank);
       Link *old = FindLink(nl.rank);
-      if (old != nullptr) { old->sock.Close(); old->sock = nl.sock; } else { links_.push_back(nl); }
+      if (old != nullptr) { old->sock.Close(); old->sock = nl.sock; old->hup_seen = false; } else { links_.push_back(nl); }
     }
     listener.Close();
 
@@ -329,10 +348,7 @@ Status HostComm::AllreduceTree(void *buf_, size_t eb, size_t count, ReduceFuncti
     }
     // a neighbour this primitive does not talk to may have died: nothing would ever wake us up, so probe
     // all links whenever nothing moved for a while
-    if (poll.Poll(kProbeMs) == 0) {
-      if (LinksBroken()) return Status::kPeerClosed;
-      continue;
-    }
+    if (!WaitLinks(&poll)) return Status::kPeerClosed;
     // up: children -> staging
     for (Child &c : kids) {
       if (c.recvd < total && c.recvd - reduced < cap && poll.CheckRead(c.l->sock.fd)) {
@@ -406,10 +422,7 @@ Status HostComm::Broadcast(void *buf_, size_t size, int root) {
     }
     // a neighbour this primitive does not talk to may have died: nothing would ever wake us up, so probe
     // all links whenever nothing moved for a while
-    if (poll.Poll(kProbeMs) == 0) {
-      if (LinksBroken()) return Status::kPeerClosed;
-      continue;
-    }
+    if (!WaitLinks(&poll)) return Status::kPeerClosed;
     if (upstream == -1) {
       for (int i = 0; i < nl && upstream == -1; ++i) {
         if (!poll.CheckRead(tree_[i]->sock.fd)) continue;
@@ -455,10 +468,7 @@ Status HostComm::AllgatherRing(void *buf_, size_t total, size_t slice_begin, siz
     if (sent < sendable) poll.WatchWrite(ring_prev_->sock.fd);
     // a neighbour this primitive does not talk to may have died: nothing would ever wake us up, so probe
     // all links whenever nothing moved for a while
-    if (poll.Poll(kProbeMs) == 0) {
-      if (LinksBroken()) return Status::kPeerClosed;
-      continue;
-    }
+    if (!WaitLinks(&poll)) return Status::kPeerClosed;
     if (recvd < total_recv && poll.CheckRead(ring_next_->sock.fd)) {
       const size_t pos = (slice_end + recvd) % total;
       size_t got; Status s = RecvSome(ring_next_, buf + pos, std::min(total_recv - recvd, total - pos), &got);
@@ -506,10 +516,7 @@ Status HostComm::ReduceScatterRing(void *buf_, size_t eb, size_t count, ReduceFu
     if (sent < sendable) poll.WatchWrite(ring_prev_->sock.fd);
     // a neighbour this primitive does not talk to may have died: nothing would ever wake us up, so probe
     // all links whenever nothing moved for a while
-    if (poll.Poll(kProbeMs) == 0) {
-      if (LinksBroken()) return Status::kPeerClosed;
-      continue;
-    }
+    if (!WaitLinks(&poll)) return Status::kPeerClosed;
     if (can_read && poll.CheckRead(ring_next_->sock.fd)) {
       const size_t off = recvd % cap;
       size_t want = std::min(total_recv - recvd, cap - (recvd - reduced));
@@ -574,10 +581,7 @@ Status HostComm::RelayImpl(Link *from, Link *to, void *buf_, size_t size) {
     if (sent < recvd) poll.WatchWrite(to->sock.fd);
     // a neighbour this primitive does not talk to may have died: nothing would ever wake us up, so probe
     // all links whenever nothing moved for a while
-    if (poll.Poll(kProbeMs) == 0) {
-      if (LinksBroken()) return Status::kPeerClosed;
-      continue;
-    }
+    if (!WaitLinks(&poll)) return Status::kPeerClosed;
     if (recvd < size && poll.CheckRead(from->sock.fd)) {
       size_t got; Status s = RecvSome(from, buf + recvd, size - recvd, &got);
       if (!Ok(s)) return s;
@@ -619,10 +623,7 @@ Status HostComm::RingShift(const void *send_, size_t nsend, void *recv_, size_t 
     if (sent < nsend) poll.WatchWrite(to->sock.fd);
     // a neighbour this primitive does not talk to may have died: nothing would ever wake us up, so probe
     // all links whenever nothing moved for a while
-    if (poll.Poll(kProbeMs) == 0) {
-      if (LinksBroken()) return Status::kPeerClosed;
-      continue;
-    }
+    if (!WaitLinks(&poll)) return Status::kPeerClosed;
     if (recvd < nrecv && poll.CheckRead(from->sock.fd)) {
       size_t got; Status s = RecvSome(from, recv + recvd, nrecv - recvd, &got);
       if (!Ok(s)) return s;

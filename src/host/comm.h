@@ -43,6 +43,8 @@ const char *LastSocketWhat();
 struct Link {
   utils::TCPSocket sock;
   int rank = -1;
+  /*! \brief the peer has closed with bytes still unread (payload, or its bye): stop watching for the hang-up */
+  bool hup_seen = false;
 };
 
 class HostComm {
@@ -78,6 +80,12 @@ class HostComm {
    *  dead process becomes an abort of the kernel within milliseconds.
    */
   bool LinksBroken();
+  /*!
+   * \brief poll the sockets a primitive watches PLUS the hang-up of every link, so that the death of a neighbour
+   *  the primitive does not talk to ends the wait at once instead of at the next idle probe.
+   * \return false when a link is dead
+   */
+  bool WaitLinks(utils::PollHelper *poll);
   /*! \brief tell the tracker this rank is done */
   void SendShutdown();
   /*! \brief log line on the tracker, or stdout without one */

@@ -77,13 +77,17 @@ bool BaseEngine::Init(int argc, char *argv[]) {
       utils::HandleLogInfo("[%d] init: CUDA context + backend set-up %.1f ms (attempt %d)\n", comm_.rank,
                            (utils::GetTime() - t_dev) * 1e3, comm_.cfg.num_trial);
     }
-    // (a link that breaks this early is fatal here; the robust engine re-joins instead, see RobustEngine::Init)
-    utils::Check(this->AttachDevice() != AttachResult::kLinkError, "lost a peer while setting up the device arena");
+    this->AttachAfterStart();
   } else {
     device_.reset();
   }
   initialized_ = true;
   return true;
+}
+
+void BaseEngine::AttachAfterStart() {
+  // (a peer that dies this early is fatal for an engine without recovery; RobustEngine re-joins instead)
+  utils::Check(this->AttachDevice() != AttachResult::kLinkError, "lost a peer while setting up the device arena");
 }
 
 BaseEngine::AttachResult BaseEngine::AttachDevice() {

@@ -109,6 +109,8 @@ class BaseEngine : public IEngine {
   enum class AttachResult { kAttached, kNoDevice, kLinkError };
   /*! \brief agree with all ranks on using the device backend, then build the arena (or drop it everywhere) */
   AttachResult AttachDevice();
+  /*! \brief the device bootstrap that follows the FIRST rendezvous of this process (Init) */
+  virtual void AttachAfterStart();
 
  protected:
   /*! \brief Hadoop streaming status line (reference allreduce_base.h:248-253) */
@@ -268,6 +270,9 @@ class RobustEngine : public BaseEngine {
   void StartWatchdog();
   void StopWatchdog();
   void Rejoin();
+  /*! \brief a peer may die while this process is still in Init (it is the replacement of another one, or the job is
+   *  just starting): that is one more recovery, not the end of this worker */
+  void AttachAfterStart() override;
 
   // ---- data movers run by every rank once Decide() says so ----
   Status ServeResult(void *buf, size_t size, uint32_t seq, bool requester);

@@ -75,6 +75,17 @@ bool RobustEngine::Shutdown(void) {
   }
 }
 
+void RobustEngine::AttachAfterStart() {
+  if (this->AttachDevice() != AttachResult::kLinkError) return;
+  ++recover_counter_;
+  in_sync_ = false;
+  if (comm_.cfg.debug) {
+    utils::HandleLogInfo("[%d] a peer vanished during the device bootstrap of Init, re-joining\n", comm_.rank);
+  }
+  StartWatchdog();
+  this->Rejoin();
+}
+
 void RobustEngine::InitAfterException(void) {
   // the caller swallowed an engine exception and wants to carry on in this process
   this->Rejoin();
@@ -103,7 +114,8 @@ void RobustEngine::Rejoin() {
     const AttachResult r = this->AttachDevice();
     if (r == AttachResult::kLinkError) {
       if (comm_.cfg.debug) {
-        utils::HandleLogInfo("[%d] a link broke while the device arena was being re-attached, re-joining again\n", comm_.rank);
+        utils::HandleLogInfo("[%d] a link broke while the device arena was being re-attached (%s), re-joining again\n",
+                             comm_.rank, LastSocketWhat());
       }
       continue;
     }

@@ -10,3 +10,13 @@ from chaos_harness import run
 def test_random_sigkills(built, seed):
     ok, info = run(seed)
     assert ok, {k: info[k] for k in ("prog", "world", "args", "kills", "done", "tails")}
+
+
+@pytest.mark.parametrize("seed", [2344, 2568, 2584])
+def test_random_sigkills_device_side(built, seed):
+    """The same with the engine's device side active on the host-memory stand-in of the backend (src/host/fake_device.cc):
+    result cache in backend memory, host buffers through the backend, recovery payloads over the backend's transport.
+    These seeds kill a rank during Init's arena bootstrap and used to end in a fatal error / a re-join livelock."""
+    ok, info = run(seed, ("model_recover", "lazy_recover", "local_recover"),
+                   extra_args=["rabit_device=fake", "rabit_device_host_min=1", "rabit_device_blob_min=1"])
+    assert ok, {k: info[k] for k in ("prog", "world", "args", "kills", "done", "tails")}
