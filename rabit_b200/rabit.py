@@ -130,18 +130,22 @@ def finalize():
 
 
 def get_rank():
+    """Rank of this process, 0 .. world size - 1 (assigned by the tracker, stable across restarts)."""
     return _LIB.RabitGetRank()
 
 
 def get_world_size():
+    """Number of ranks in the job (1 without a tracker)."""
     return _LIB.RabitGetWorldSize()
 
 
 def is_distributed():
+    """True when a tracker is configured, False for a single stand-alone process."""
     return bool(_LIB.RabitIsDistributed())
 
 
 def get_ring_prev_rank():
+    """Rank of the ring predecessor (whose local model this rank keeps a replica of)."""
     return _LIB.RabitGetRingPrevRank()
 
 
@@ -158,6 +162,7 @@ def tracker_print(msg):
 
 
 def get_processor_name():
+    """Host name of this worker."""
     buf = ctypes.create_string_buffer(256)
     n = ctypes.c_ulong()
     _LIB.RabitGetProcessorName(buf, ctypes.byref(n), 256)

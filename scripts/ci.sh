@@ -4,6 +4,7 @@
 set -euo pipefail
 cd "$(dirname "$0")/.."
 python scripts/lint.py
+python scripts/gen_api_doc.py --check   # doc/{cpp,c,python}_api.md are generated from the sources
 python build.py
 ./build/bin/unit_tests
 python -m pytest tests -x -q -m "not gpu"
