@@ -502,6 +502,12 @@ def run_ours(args):
             store.set("bench_recovery_done", "1")
         else:
             store.get("bench_recovery_done")
+    same_prog = None
+    if not args.no_recovery and n > 1 and store is not None:
+        try:
+            same_prog = same_program_on_this_library(rank, world, local, store, S, max(1, min(args.steps, 5)))
+        except Exception as e:  # pylint: disable=broad-except
+            same_prog = {"error": str(e)[:200]}
     if rank == 0:
         bus = 2.0 * (n - 1) / n
 
@@ -551,6 +557,8 @@ def run_ours(args):
         if sweep:
             out["sweep"] = sweep
             out["histogram_pair_sum_f64_4MB"] = hist
+        if same_prog is not None:
+            out["same_program"] = same_prog
         if recovery is not None:
             out["recovery"] = recovery
             if "recover_s_per_kill" in recovery:
@@ -682,28 +690,59 @@ def timed_nccl(dist, torch, t, steps, warmup, rabit, np, kind="allreduce", rank=
 
 
 # ---------------------------------------------------------------------- reference
-def ref_run(exe, argv, rank, world, store, tag, timeout=3000):
-    """all torchrun ranks start one reference worker each under a fresh tracker; returns rank 0's REF_RESULT
-    lines (on torchrun rank 0) or None"""
+def ref_run(exe, argv, rank, world, store, tag, timeout=3000, env_extra=None):
+    """all torchrun ranks start one worker of the program each under a fresh tracker; returns rank 0's REF_RESULT
+    lines (on torchrun rank 0) or None. A worker that fails or overruns `timeout` makes the result None, never an
+    exception or a wait without end: every rank always posts its return code."""
     tracker, port = start_tracker(rank, world, store, "ref_tracker_" + tag)
     env = dict(os.environ)
     env.update({"DMLC_TRACKER_URI": "127.0.0.1", "DMLC_TRACKER_PORT": str(port), "DMLC_TASK_ID": str(rank),
                 "DMLC_ROLE": "worker", "DMLC_NUM_ATTEMPT": "0"})
-    r = subprocess.run([exe] + argv, env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE, timeout=timeout)
+    env.update(env_extra or {})
+    rc, stdout = "failed", ""
+    try:
+        r = subprocess.run([exe] + argv, env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE, timeout=timeout)
+        rc, stdout = str(r.returncode), r.stdout.decode(errors="replace")
+        if r.returncode != 0:
+            sys.stderr.write("[bench] %s worker %d rc=%d: %s\n" % (tag, rank, r.returncode, r.stderr.decode(errors="replace")[-400:]))
+    except Exception as e:  # pylint: disable=broad-except
+        sys.stderr.write("[bench] %s worker %d: %s\n" % (tag, rank, str(e)[:200]))
     if tracker is not None:
         tracker.join(20)
         tracker.close()
     # rabit rank 0 (the one that prints) is whatever process the tracker labelled 0: route its lines to
     # torchrun rank 0 through the store
-    mine = [l for l in r.stdout.decode().splitlines() if l.startswith("REF_RESULT")]
+    mine = [l for l in stdout.splitlines() if l.startswith("REF_RESULT")]
     if mine:
         store.set("ref_result_" + tag, "\n".join(mine))
-    store.set("ref_rc_%s_%d" % (tag, rank), str(r.returncode))
+    store.set("ref_rc_%s_%d" % (tag, rank), rc)
     if rank != 0:
         return None
     if not all(store.get("ref_rc_%s_%d" % (tag, q)).decode() == "0" for q in range(world)):
         return None
     return store.get("ref_result_" + tag).decode().splitlines()
+
+
+def same_program_on_this_library(rank, world, local, store, nbytes, steps):
+    """baseline/ref_speed.cc, the harness of the reference arm, compiled UNCHANGED against this library
+    (build/bin/ours_speed): host buffers in, host buffers out (pageable std::vector), wall clock inside the program,
+    max over ranks: what a user of the reference gets by re-linking. Once with the device backend off (host engine
+    over loopback TCP, like the reference) and once with it on (the host buffers ride the GPUs: H2D | kernels | D2H)."""
+    exe = os.path.join(ROOT, "build", "bin", "ours_speed")
+    if not os.path.isfile(exe):
+        return {"error": "build/bin/ours_speed missing"} if rank == 0 else None
+    out = {"program": "baseline/ref_speed.cc (unchanged) linked with lib/librabit_mock.so, rabit_engine=robust",
+           "steps": steps, "bytes_per_rank": nbytes}
+    for tag, extra in (("host_tcp", ["rabit_device=off"]), ("via_gpus", ["rabit_device=on"])):
+        lines = ref_run(exe, [str(nbytes // 4), str(steps), "1", "rabit_engine=robust", "rabit_enable_tcp_no_delay=true"] + extra,
+                        rank, world, store, "same_" + tag, timeout=240, env_extra={"RABIT_DEVICE_ORDINAL": str(local)})
+        if rank == 0:
+            if lines:
+                ms = float(lines[0].split()[1])
+                out[tag] = {"ms_per_step": ms, "value": world * nbytes / (ms * 1e-3) / 1e9, "unit": "GB/s"}
+            else:
+                out[tag] = {"error": "run failed (see stderr)"}
+    return out if rank == 0 else None
 
 
 def run_reference(args):

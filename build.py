@@ -139,8 +139,11 @@ def build(cuda=True, verbose=False, programs=True):
         bin_dir = os.path.join(ROOT, "build", "bin")
         os.makedirs(bin_dir, exist_ok=True)
         pjobs = []
-        for src in sorted(glob.glob(os.path.join(ROOT, "guide/*.cc")) + glob.glob(os.path.join(ROOT, "test/*.cc"))):
-            name = os.path.basename(src)[:-3]
+        srcs = [(s, os.path.basename(s)[:-3]) for s in
+                sorted(glob.glob(os.path.join(ROOT, "guide/*.cc")) + glob.glob(os.path.join(ROOT, "test/*.cc")))]
+        # the harness of bench.py's reference arm, unchanged, against THIS library: the same program on both sides
+        srcs.append((os.path.join(ROOT, "baseline", "ref_speed.cc"), "ours_speed"))
+        for src, name in srcs:
             # programs that use mock= link the mock library, like the reference's test/Makefile
             lib = "rabit_mock"
             exe = os.path.join(bin_dir, name)

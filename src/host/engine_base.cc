@@ -73,6 +73,8 @@ bool BaseEngine::Init(int argc, char *argv[]) {
   if (comm_.world > 1 || comm_.cfg.device_force) {
     const double t_dev = utils::GetTime();
     if (!device_) device_.reset(DeviceBackend::Create(comm_.cfg));
+    utils::Check(device_ != nullptr || comm_.cfg.device != "on",
+                 "rabit_device=on but this rank has no usable GPU (or the library was built without CUDA)");
     if (getenv("RABIT_RECOVER_PROFILE") != nullptr) {
       utils::HandleLogInfo("[%d] init: CUDA context + backend set-up %.1f ms (attempt %d)\n", comm_.rank,
                            (utils::GetTime() - t_dev) * 1e3, comm_.cfg.num_trial);
