@@ -3,8 +3,12 @@
  */
 #include "comm.h"
 
+#include "rabit/internal/timer.h"
+
 #include <algorithm>
+#include <atomic>
 #include <cerrno>
+#include <cstddef>
 #include <map>
 
 namespace rabit {
@@ -30,29 +34,6 @@ Status ErrnoStatus() {
 }
 inline bool WouldBlock() { return errno == EAGAIN || errno == EWOULDBLOCK || errno == EINTR; }
 
-/*! \brief one non-blocking recv; *got == 0 with kOk means "nothing yet" */
-Status RecvSome(Link *l, char *p, size_t max, size_t *got) {
-  *got = 0;
-  if (max == 0) return Status::kOk;
-  ssize_t n = l->sock.Recv(p, max);
-  if (n > 0) { *got = static_cast<size_t>(n); return Status::kOk; }
-  if (n == 0) { snprintf(g_last_sock_what, sizeof(g_last_sock_what), "recv=0 from %d", l->rank); return Status::kPeerClosed; }
-  if (WouldBlock()) return Status::kOk;
-  snprintf(g_last_sock_what, sizeof(g_last_sock_what), "recv(%p,%lu) from %d", static_cast<void *>(p),
-           static_cast<unsigned long>(max), l->rank);  // NOLINT(*)
-  return ErrnoStatus();
-}
-/*! \brief one non-blocking send */
-Status SendSome(Link *l, const char *p, size_t max, size_t *put) {
-  *put = 0;
-  if (max == 0) return Status::kOk;
-  ssize_t n = l->sock.Send(p, max);
-  if (n >= 0) { *put = static_cast<size_t>(n); return Status::kOk; }
-  if (WouldBlock()) return Status::kOk;
-  snprintf(g_last_sock_what, sizeof(g_last_sock_what), "send(%p,%lu) to %d", static_cast<const void *>(p),
-           static_cast<unsigned long>(max), l->rank);  // NOLINT(*)
-  return ErrnoStatus();
-}
 /*! \brief largest multiple of unit that is <= v (at least one unit) */
 inline size_t FloorTo(size_t v, size_t unit) { return std::max(unit, v / unit * unit); }
 }  // namespace
@@ -72,7 +53,10 @@ const char *StatusName(Status s) {
 }
 
 HostComm::HostComm() {}
-HostComm::~HostComm() { this->CloseLinks(); }
+HostComm::~HostComm() {
+  this->CloseLinks();
+  if (bell_fd_ >= 0) ::close(bell_fd_);
+}
 
 void HostComm::CloseLinks(bool graceful) {
   if (graceful) {
@@ -81,7 +65,7 @@ void HostComm::CloseLinks(bool graceful) {
     const char bye = 'B';
     for (Link &l : links_) if (!l.sock.IsClosed()) l.sock.Send(&bye, 1);
   }
-  for (Link &l : links_) l.sock.Close();
+  for (Link &l : links_) { l.sock.Close(); DropShm(&l); }
   links_.clear();
   tree_.clear();
   parent_slot_ = -1;
@@ -101,10 +85,38 @@ bool HostComm::LinksBroken() {
   return false;
 }
 
-bool HostComm::WaitLinks(utils::PollHelper *poll) {
+bool HostComm::WaitLinks(WaitSet *ws) {
+  auto ring_ready = [](const WaitSet::Item &it) {
+    return it.recv ? it.l->rx.Avail() != 0 : it.l->tx.Space() >= it.l->tx.SendThreshold();
+  };
+  if (!ws->ready_now && !ws->shm.empty()) {
+    // a short look before going to sleep: the other end usually is a few microseconds away
+    if (cfg.shm_spin_us > 0) {
+      const double until = utils::GetTime() + cfg.shm_spin_us * 1e-6;
+      do {
+        for (const WaitSet::Item &it : ws->shm) if (ring_ready(it)) { ws->ready_now = true; break; }
+      } while (!ws->ready_now && utils::GetTime() < until);
+    }
+    if (!ws->ready_now) {
+      // leave the note "wake me", then look once more (see ShmRing::SetConsumerWaiting)
+      for (const WaitSet::Item &it : ws->shm) {
+        if (it.recv) it.l->rx.SetConsumerWaiting(1); else it.l->tx.SetProducerWaiting(1);
+      }
+      for (const WaitSet::Item &it : ws->shm) if (ring_ready(it)) { ws->ready_now = true; break; }
+    }
+  }
+  // bytes are waiting in shared memory and no socket needs asking: nothing to ask the kernel
+  if (ws->ready_now && !ws->tcp) return true;
+  utils::PollHelper *poll = &ws->poll;
+  if (!ws->shm.empty() && bell_fd_ >= 0) poll->WatchRead(bell_fd_);
   for (Link &l : links_) if (!l.hup_seen && !l.sock.IsClosed()) poll->WatchHangup(l.sock.fd);
   // nothing moved for a while: a peer can also vanish without a FIN reaching us (host down), so look at every link
-  if (poll->Poll(kProbeMs) == 0) return !LinksBroken();
+  const int rc = poll->Poll(ws->ready_now ? 0 : kProbeMs);
+  if (!ws->shm.empty() && bell_fd_ >= 0 && poll->CheckRead(bell_fd_)) {
+    char drain[64];
+    while (recv(bell_fd_, drain, sizeof(drain), MSG_DONTWAIT) > 0) {}
+  }
+  if (rc == 0) return ws->ready_now || !LinksBroken();
   for (Link &l : links_) {
     if (l.hup_seen || l.sock.IsClosed() || !poll->CheckHangup(l.sock.fd)) continue;
     char c;
@@ -118,6 +130,84 @@ bool HostComm::WaitLinks(utils::PollHelper *poll) {
     l.hup_seen = true;
   }
   return true;
+}
+
+// ---------------------------------------------------------------- link I/O
+/*! \brief one non-blocking receive; *got == 0 with kOk means "nothing yet" */
+Status HostComm::RecvSome(Link *l, char *p, size_t max, size_t *got) {
+  *got = 0;
+  if (max == 0) return Status::kOk;
+  if (l->shm) {
+    *got = l->rx.Read(p, max);
+    // a producer that went to sleep on a full ring is woken once a worthwhile piece is free again
+    if (*got != 0 && l->rx.Space() >= l->rx.SendThreshold() && l->rx.TakeProducerWaiting()) RingBell(l);
+    return Status::kOk;
+  }
+  ssize_t n = l->sock.Recv(p, max);
+  if (n > 0) { *got = static_cast<size_t>(n); return Status::kOk; }
+  if (n == 0) { snprintf(g_last_sock_what, sizeof(g_last_sock_what), "recv=0 from %d", l->rank); return Status::kPeerClosed; }
+  if (WouldBlock()) return Status::kOk;
+  snprintf(g_last_sock_what, sizeof(g_last_sock_what), "recv(%p,%lu) from %d", static_cast<void *>(p),
+           static_cast<unsigned long>(max), l->rank);  // NOLINT(*)
+  return ErrnoStatus();
+}
+
+/*! \brief one non-blocking send */
+Status HostComm::SendSome(Link *l, const char *p, size_t max, size_t *put) {
+  *put = 0;
+  if (max == 0) return Status::kOk;
+  if (l->shm) {
+    *put = l->tx.Write(p, max);
+    if (*put != 0 && l->tx.TakeConsumerWaiting()) RingBell(l);
+    return Status::kOk;
+  }
+  ssize_t n = l->sock.Send(p, max);
+  if (n >= 0) { *put = static_cast<size_t>(n); return Status::kOk; }
+  if (WouldBlock()) return Status::kOk;
+  snprintf(g_last_sock_what, sizeof(g_last_sock_what), "send(%p,%lu) to %d", static_cast<const void *>(p),
+           static_cast<unsigned long>(max), l->rank);  // NOLINT(*)
+  return ErrnoStatus();
+}
+
+void HostComm::RingBell(Link *l) {
+  // (a full queue means wake-ups are already pending; a vanished peer is the hang-up watch's business)
+  if (bell_fd_ >= 0 && l->bell_len != 0) {
+    const char c = 1;
+    sendto(bell_fd_, &c, 1, MSG_DONTWAIT | MSG_NOSIGNAL, reinterpret_cast<const sockaddr *>(&l->bell), l->bell_len);
+  }
+}
+
+void HostComm::ReplaceLink(Link *l, const Link &fresh) {
+  l->sock.Close();
+  DropShm(l);
+  *l = fresh;      // socket, rings and doorbell of the new connection (plain handles: the copy owns them now)
+}
+
+void HostComm::DropShm(Link *l) {
+  l->tx.Close();
+  l->rx.Close();
+  l->shm = false;
+  l->bell_len = 0;
+}
+
+void HostComm::WantRecv(WaitSet *ws, Link *l) {
+  if (!l->shm) { ws->poll.WatchRead(l->sock.fd); ws->tcp = true; return; }
+  ws->shm.push_back(WaitSet::Item{l, true});
+  if (l->rx.Avail() != 0) ws->ready_now = true;
+}
+
+void HostComm::WantSend(WaitSet *ws, Link *l) {
+  if (!l->shm) { ws->poll.WatchWrite(l->sock.fd); ws->tcp = true; return; }
+  ws->shm.push_back(WaitSet::Item{l, false});
+  if (l->tx.Space() >= l->tx.SendThreshold()) ws->ready_now = true;
+}
+
+bool HostComm::CanRecv(const WaitSet &ws, Link *l) const {
+  return l->shm ? l->rx.Avail() != 0 : ws.poll.CheckRead(l->sock.fd);
+}
+
+bool HostComm::CanSend(const WaitSet &ws, Link *l) const {
+  return l->shm ? l->tx.Space() >= l->tx.SendThreshold() : ws.poll.CheckWrite(l->sock.fd);
 }
 
 Link *HostComm::FindLink(int r) {
@@ -173,6 +263,7 @@ bool HostComm::Connect(const char *cmd) {
     }
     utils::Check(t.RecvInt(&ring_prev_rank) && t.RecvInt(&ring_next_rank), "tracker: cannot read ring");
 
+    this->OpenDoorbell();
     utils::TCPSocket listener;
     struct CloseOnExit { utils::TCPSocket *s; ~CloseOnExit() { s->Close(); } } close_listener{&listener};
     listener.Create();
@@ -209,13 +300,14 @@ bool HostComm::Connect(const char *cmd) {
         // handshake: who I am, whom I mean to reach (a stale address in the tracker's table can belong to a
         // different worker by now: ephemeral ports are recycled quickly), and who answered
         int echoed = -1;
-        if (!nl.sock.SendInt(rank) || !nl.sock.SendInt(peer_rank) || !nl.sock.RecvInt(&echoed) || echoed != peer_rank) {
+        nl.rank = peer_rank;
+        if (!nl.sock.SendInt(rank) || !nl.sock.SendInt(peer_rank) || !nl.sock.RecvInt(&echoed) || echoed != peer_rank ||
+            !NegotiateSharedMemory(&nl, true)) {
           nl.sock.Close(); ++nerr; continue;
         }
         dialled.push_back(peer_rank);
-        nl.rank = peer_rank;
         Link *old = FindLink(peer_rank);
-        if (old != nullptr) { old->sock.Close(); old->sock = nl.sock; old->hup_seen = false; } else { links_.push_back(nl); }
+        if (old != nullptr) ReplaceLink(old, nl); else links_.push_back(nl);
       }
       utils::Check(t.SendInt(nerr), "tracker: send failed");
     } while (nerr != 0);
@@ -242,7 +334,7 @@ bool HostComm::Connect(const char *cmd) {
       nl.sock = listener.Accept();
       int intended = -1;
       if (!nl.sock.SendInt(rank) || !nl.sock.RecvInt(&nl.rank) || !nl.sock.RecvInt(&intended) || intended != rank ||
-          std::find(expected.begin(), expected.end(), nl.rank) == expected.end()) {
+          std::find(expected.begin(), expected.end(), nl.rank) == expected.end() || !NegotiateSharedMemory(&nl, false)) {
         nl.sock.Close();  // dialler died, or was sent here by mistake
         continue;
       }
@@ -252,7 +344,7 @@ bool HostComm::Connect(const char *cmd) {
                          std::find(accepted.begin(), accepted.end(), nl.rank) != accepted.end();
       if (!known) accepted.push_back(nl.rank);
       Link *old = FindLink(nl.rank);
-      if (old != nullptr) { old->sock.Close(); old->sock = nl.sock; old->hup_seen = false; } else { links_.push_back(nl); }
+      if (old != nullptr) ReplaceLink(old, nl); else links_.push_back(nl);
     }
     listener.Close();
 
@@ -278,11 +370,84 @@ bool HostComm::Connect(const char *cmd) {
   } catch (const std::exception &e) {
     fprintf(stderr, "[rabit] rendezvous (%s) failed: %s\n", cmd, e.what());
     // leave nothing half-built behind: the caller retries from scratch
-    for (Link &l : links_) l.sock.Close();
+    for (Link &l : links_) { l.sock.Close(); DropShm(&l); }
     links_.clear();
     tree_.clear(); parent_slot_ = -1; ring_prev_ = ring_next_ = nullptr;
     return false;
   }
+}
+
+// ------------------------------------------------------ same-host data plane
+namespace {
+/*! \brief what the two ends of a fresh connection tell each other right after the rendezvous */
+struct ShmHello {
+  uint32_t magic;
+  uint32_t want;        // this end is able and willing to use shared memory
+  uint64_t token[2];    // HostToken(): equal on both ends = same host, same namespaces, same user
+  int32_t pid;
+  int32_t ring_fd;      // the sender's ring (this end -> peer) is file descriptor ring_fd of process pid
+  uint64_t capacity;
+  char bell[48];        // abstract unix datagram address of this end's doorbell (without the leading NUL)
+};
+const uint32_t kHelloMagic = 0x52424c31;  // "RBL1"
+}  // namespace
+
+void HostComm::OpenDoorbell() {
+  if (bell_fd_ >= 0 || cfg.shm_ring < (64 << 10)) return;
+  static std::atomic<int> serial{0};
+  bell_fd_ = socket(AF_UNIX, SOCK_DGRAM | SOCK_NONBLOCK | SOCK_CLOEXEC, 0);
+  bell_name_ = "rabit-bell-" + std::to_string(getpid()) + "-" + std::to_string(serial.fetch_add(1));
+  sockaddr_un a; std::memset(&a, 0, sizeof(a));
+  a.sun_family = AF_UNIX;
+  std::memcpy(a.sun_path + 1, bell_name_.data(), bell_name_.size());
+  if (bell_fd_ < 0 || bind(bell_fd_, reinterpret_cast<sockaddr *>(&a),
+                           static_cast<socklen_t>(offsetof(sockaddr_un, sun_path) + 1 + bell_name_.size())) != 0) {
+    if (bell_fd_ >= 0) ::close(bell_fd_);
+    bell_fd_ = -1;
+  }
+}
+
+/*!
+ * \brief second half of the dial / accept handshake of one connection: both ends say whether they can share memory
+ *  (same host, namespaces and user), show each other their ring, and confirm. It runs while BOTH ends are busy with
+ *  exactly this connection (the dialler right after connect(), the acceptor right after accept()), so it never waits
+ *  for a third worker. false = the connection broke.
+ */
+bool HostComm::NegotiateSharedMemory(Link *l, bool dialler) {
+  const size_t capacity = cfg.shm_ring / 4096 * 4096;
+  ShmHello mine; std::memset(&mine, 0, sizeof(mine));
+  mine.magic = kHelloMagic;
+  HostToken(mine.token);
+  mine.pid = static_cast<int32_t>(getpid());
+  mine.capacity = capacity;
+  snprintf(mine.bell, sizeof(mine.bell), "%s", bell_name_.c_str());
+  mine.want = bell_fd_ >= 0 && capacity >= (64 << 10) && l->tx.Create(capacity) ? 1u : 0u;
+  mine.ring_fd = l->tx.fd();
+  if (cfg.tcp_no_delay) l->sock.SetNoDelay(true);
+  ShmHello peer;
+  auto send_hello = [&]() { return l->sock.SendAll(&mine, sizeof(mine)) == sizeof(mine); };
+  auto recv_hello = [&]() { return l->sock.RecvAll(&peer, sizeof(peer)) == sizeof(peer) && peer.magic == kHelloMagic; };
+  if (dialler ? !(send_hello() && recv_hello()) : !(recv_hello() && send_hello())) { DropShm(l); return false; }
+  peer.bell[sizeof(peer.bell) - 1] = '\0';
+  const size_t blen = strlen(peer.bell);
+  char ok = 0, peer_ok = 0;
+  if (mine.want != 0 && peer.want != 0 && peer.token[0] == mine.token[0] && peer.token[1] == mine.token[1] &&
+      peer.capacity == capacity && blen != 0 && l->rx.Open(peer.pid, peer.ring_fd, capacity)) {
+    std::memset(&l->bell, 0, sizeof(l->bell));
+    l->bell.sun_family = AF_UNIX;
+    std::memcpy(l->bell.sun_path + 1, peer.bell, blen);
+    l->bell_len = static_cast<socklen_t>(offsetof(sockaddr_un, sun_path) + 1 + blen);
+    ok = 1;
+  }
+  auto send_ok = [&]() { return l->sock.SendAll(&ok, 1) == 1; };
+  auto recv_ok = [&]() { return l->sock.RecvAll(&peer_ok, 1) == 1; };
+  if (dialler ? !(send_ok() && recv_ok()) : !(recv_ok() && send_ok())) { DropShm(l); return false; }
+  if (ok != 0 && peer_ok != 0) {
+    l->shm = true;
+  } else {
+    DropShm(l);
+  }
+  return true;
 }
 
 void HostComm::SendShutdown() {
@@ -331,27 +496,27 @@ Status HostComm::AllreduceTree(void *buf_, size_t eb, size_t count, ReduceFuncti
   size_t reduced = kids.empty() ? total : 0;  // prefix of buf that holds the subtree's reduction
   size_t sent_up = 0, recv_down = 0;
   const MPI::Datatype dtype(eb);
-  utils::PollHelper poll;
+  WaitSet ws;
   while (true) {
     if (is_root) { sent_up = reduced; recv_down = reduced; }
     bool done = recv_down == total;
     for (const Child &c : kids) done = done && c.sent_down == total;
     if (done) break;
-    poll.Clear();
+    ws.Clear();
     for (const Child &c : kids) {
-      if (c.recvd < total && c.recvd - reduced < cap) poll.WatchRead(c.l->sock.fd);
-      if (c.sent_down < recv_down) poll.WatchWrite(c.l->sock.fd);
+      if (c.recvd < total && c.recvd - reduced < cap) WantRecv(&ws, c.l);
+      if (c.sent_down < recv_down) WantSend(&ws, c.l);
     }
     if (parent != nullptr) {
-      if (sent_up < reduced) poll.WatchWrite(parent->sock.fd);
-      if (recv_down < sent_up) poll.WatchRead(parent->sock.fd);
+      if (sent_up < reduced) WantSend(&ws, parent);
+      if (recv_down < sent_up) WantRecv(&ws, parent);
     }
     // a neighbour this primitive does not talk to may have died: nothing would ever wake us up, so probe
     // all links whenever nothing moved for a while
-    if (!WaitLinks(&poll)) return Status::kPeerClosed;
+    if (!WaitLinks(&ws)) return Status::kPeerClosed;
     // up: children -> staging
     for (Child &c : kids) {
-      if (c.recvd < total && c.recvd - reduced < cap && poll.CheckRead(c.l->sock.fd)) {
+      if (c.recvd < total && c.recvd - reduced < cap && CanRecv(ws, c.l)) {
         const size_t off = c.recvd % cap;
         size_t want = std::min(total - c.recvd, cap - (c.recvd - reduced));
         want = std::min(want, cap - off);
@@ -376,12 +541,12 @@ Status HostComm::AllreduceTree(void *buf_, size_t eb, size_t count, ReduceFuncti
       }
     }
     if (parent != nullptr) {
-      if (sent_up < reduced && poll.CheckWrite(parent->sock.fd)) {
+      if (sent_up < reduced && CanSend(ws, parent)) {
         size_t put; Status s = SendSome(parent, buf + sent_up, reduced - sent_up, &put);
         if (!Ok(s)) return s;
         sent_up += put;
       }
-      if (recv_down < sent_up && poll.CheckRead(parent->sock.fd)) {
+      if (recv_down < sent_up && CanRecv(ws, parent)) {
         size_t got; Status s = RecvSome(parent, buf + recv_down, sent_up - recv_down, &got);
         if (!Ok(s)) return s;
         recv_down += got;
@@ -391,7 +556,7 @@ Status HostComm::AllreduceTree(void *buf_, size_t eb, size_t count, ReduceFuncti
     }
     // down: final values -> children
     for (Child &c : kids) {
-      if (c.sent_down < recv_down && poll.CheckWrite(c.l->sock.fd)) {
+      if (c.sent_down < recv_down && CanSend(ws, c.l)) {
         size_t put; Status s = SendSome(c.l, buf + c.sent_down, recv_down - c.sent_down, &put);
         if (!Ok(s)) return s;
         c.sent_down += put;
@@ -409,36 +574,35 @@ Status HostComm::Broadcast(void *buf_, size_t size, int root) {
   int upstream = (rank == root) ? -2 : -1;
   size_t recvd = (rank == root) ? size : 0;
   std::vector<size_t> sent(nl, 0);
-  utils::PollHelper poll;
+  WaitSet ws;
   while (true) {
     bool done = recvd == size;
     for (int i = 0; i < nl; ++i) if (i != upstream) done = done && sent[i] == size;
     if (done) break;
-    poll.Clear();
+    ws.Clear();
     for (int i = 0; i < nl; ++i) {
-      const int fd = tree_[i]->sock.fd;
-      if (upstream == -1 || (i == upstream && recvd < size)) poll.WatchRead(fd);
-      if (upstream != -1 && i != upstream && sent[i] < recvd) poll.WatchWrite(fd);
+      if (upstream == -1 || (i == upstream && recvd < size)) WantRecv(&ws, tree_[i]);
+      if (upstream != -1 && i != upstream && sent[i] < recvd) WantSend(&ws, tree_[i]);
     }
     // a neighbour this primitive does not talk to may have died: nothing would ever wake us up, so probe
     // all links whenever nothing moved for a while
-    if (!WaitLinks(&poll)) return Status::kPeerClosed;
+    if (!WaitLinks(&ws)) return Status::kPeerClosed;
     if (upstream == -1) {
       for (int i = 0; i < nl && upstream == -1; ++i) {
-        if (!poll.CheckRead(tree_[i]->sock.fd)) continue;
+        if (!CanRecv(ws, tree_[i])) continue;
         size_t got; Status s = RecvSome(tree_[i], buf, size, &got);
         if (!Ok(s)) return s;
         if (got != 0) { upstream = i; recvd = got; }
       }
       continue;  // re-arm the poll set now that directions are known
     }
-    if (upstream >= 0 && recvd < size && poll.CheckRead(tree_[upstream]->sock.fd)) {
+    if (upstream >= 0 && recvd < size && CanRecv(ws, tree_[upstream])) {
       size_t got; Status s = RecvSome(tree_[upstream], buf + recvd, size - recvd, &got);
       if (!Ok(s)) return s;
       recvd += got;
     }
     for (int i = 0; i < nl; ++i) {
-      if (i == upstream || sent[i] >= recvd || !poll.CheckWrite(tree_[i]->sock.fd)) continue;
+      if (i == upstream || sent[i] >= recvd || !CanSend(ws, tree_[i])) continue;
       size_t put; Status s = SendSome(tree_[i], buf + sent[i], recvd - sent[i], &put);
       if (!Ok(s)) return s;
       sent[i] += put;
@@ -460,22 +624,22 @@ Status HostComm::AllgatherRing(void *buf_, size_t total, size_t slice_begin, siz
   const size_t total_recv = total - mine;
   const size_t total_send = total - size_prev_slice;
   size_t recvd = 0, sent = 0;
-  utils::PollHelper poll;
+  WaitSet ws;
   while (recvd < total_recv || sent < total_send) {
     const size_t sendable = std::min(total_send, mine + recvd);
-    poll.Clear();
-    if (recvd < total_recv) poll.WatchRead(ring_next_->sock.fd);
-    if (sent < sendable) poll.WatchWrite(ring_prev_->sock.fd);
+    ws.Clear();
+    if (recvd < total_recv) WantRecv(&ws, ring_next_);
+    if (sent < sendable) WantSend(&ws, ring_prev_);
     // a neighbour this primitive does not talk to may have died: nothing would ever wake us up, so probe
     // all links whenever nothing moved for a while
-    if (!WaitLinks(&poll)) return Status::kPeerClosed;
-    if (recvd < total_recv && poll.CheckRead(ring_next_->sock.fd)) {
+    if (!WaitLinks(&ws)) return Status::kPeerClosed;
+    if (recvd < total_recv && CanRecv(ws, ring_next_)) {
       const size_t pos = (slice_end + recvd) % total;
       size_t got; Status s = RecvSome(ring_next_, buf + pos, std::min(total_recv - recvd, total - pos), &got);
       if (!Ok(s)) return s;
       recvd += got;
     }
-    if (sent < sendable && poll.CheckWrite(ring_prev_->sock.fd)) {
+    if (sent < sendable && CanSend(ws, ring_prev_)) {
       const size_t pos = (slice_begin + sent) % total;
       size_t put; Status s = SendSome(ring_prev_, buf + pos, std::min(sendable - sent, total - pos), &put);
       if (!Ok(s)) return s;
@@ -507,17 +671,42 @@ Status HostComm::ReduceScatterRing(void *buf_, size_t eb, size_t count, ReduceFu
   char *stage = scratch_.data();
   size_t recvd = 0, reduced = 0, sent = 0;
   const MPI::Datatype dtype(eb);
-  utils::PollHelper poll;
+  WaitSet ws;
   while (sent < total_send || reduced < total_recv) {
     size_t sendable = std::min(total_send, head + reduced);
-    poll.Clear();
+    ws.Clear();
     const bool can_read = recvd < total_recv && recvd - reduced < cap;
-    if (can_read) poll.WatchRead(ring_next_->sock.fd);
-    if (sent < sendable) poll.WatchWrite(ring_prev_->sock.fd);
+    if (can_read) WantRecv(&ws, ring_next_);
+    if (sent < sendable) WantSend(&ws, ring_prev_);
     // a neighbour this primitive does not talk to may have died: nothing would ever wake us up, so probe
     // all links whenever nothing moved for a while
-    if (!WaitLinks(&poll)) return Status::kPeerClosed;
-    if (can_read && poll.CheckRead(ring_next_->sock.fd)) {
+    if (!WaitLinks(&ws)) return Status::kPeerClosed;
+    if (can_read && ring_next_->shm) {
+      // fold straight out of the shared-memory ring: no staging copy. One contiguous span per turn, so that the
+      // partial sums it produces leave for the predecessor before the next span is folded.
+      ShmRing &rx = ring_next_->rx;
+      const char *span;
+      size_t len = std::min(rx.Peek(&span), total_recv - reduced);
+      const size_t pos = (recv_start + reduced) % total;
+      len = std::min(len, total - pos) / eb * eb;
+      bool copied = false;
+      if (len == 0 && std::min(rx.Avail(), total_recv - reduced) >= eb) {
+        // an item that straddles the wrap of the ring goes through a copy
+        if (item_.size() < eb) item_.resize(eb);
+        rx.Read(item_.data(), eb);
+        span = item_.data();
+        len = eb;
+        copied = true;
+      }
+      if (len != 0) {
+        if (src != nullptr) std::memcpy(buf + pos, src + pos, len);
+        reducer(span, buf + pos, static_cast<int>(len / eb), dtype);
+        if (!copied) rx.Consume(len);
+        if (rx.Space() >= rx.SendThreshold() && rx.TakeProducerWaiting()) RingBell(ring_next_);
+        reduced += len;
+      }
+      recvd = reduced;
+    } else if (can_read && CanRecv(ws, ring_next_)) {
       const size_t off = recvd % cap;
       size_t want = std::min(total_recv - recvd, cap - (recvd - reduced));
       want = std::min(want, cap - off);
@@ -536,7 +725,7 @@ Status HostComm::ReduceScatterRing(void *buf_, size_t eb, size_t count, ReduceFu
       reduced += len;
     }
     sendable = std::min(total_send, head + reduced);
-    if (sent < sendable && poll.CheckWrite(ring_prev_->sock.fd)) {
+    if (sent < sendable && CanSend(ws, ring_prev_)) {
       const size_t pos = (send_start + sent) % total;
       // the first `head` bytes of the stream are our own untouched data, the rest are folded partial sums
       const bool own = src != nullptr && sent < head;
@@ -574,20 +763,20 @@ Status HostComm::RelayImpl(Link *from, Link *to, void *buf_, size_t size) {
   char *buf = static_cast<char *>(buf_);
   size_t recvd = from != nullptr ? 0 : size;
   size_t sent = to != nullptr ? 0 : size;
-  utils::PollHelper poll;
+  WaitSet ws;
   while (recvd < size || sent < size) {
-    poll.Clear();
-    if (recvd < size) poll.WatchRead(from->sock.fd);
-    if (sent < recvd) poll.WatchWrite(to->sock.fd);
+    ws.Clear();
+    if (recvd < size) WantRecv(&ws, from);
+    if (sent < recvd) WantSend(&ws, to);
     // a neighbour this primitive does not talk to may have died: nothing would ever wake us up, so probe
     // all links whenever nothing moved for a while
-    if (!WaitLinks(&poll)) return Status::kPeerClosed;
-    if (recvd < size && poll.CheckRead(from->sock.fd)) {
+    if (!WaitLinks(&ws)) return Status::kPeerClosed;
+    if (recvd < size && CanRecv(ws, from)) {
       size_t got; Status s = RecvSome(from, buf + recvd, size - recvd, &got);
       if (!Ok(s)) return s;
       recvd += got;
     }
-    if (sent < recvd && poll.CheckWrite(to->sock.fd)) {
+    if (sent < recvd && CanSend(ws, to)) {
       size_t put; Status s = SendSome(to, buf + sent, recvd - sent, &put);
       if (!Ok(s)) return s;
       sent += put;
@@ -616,20 +805,20 @@ Status HostComm::RingShift(const void *send_, size_t nsend, void *recv_, size_t 
   const char *send = static_cast<const char *>(send_);
   char *recv = static_cast<char *>(recv_);
   size_t sent = 0, recvd = 0;
-  utils::PollHelper poll;
+  WaitSet ws;
   while (sent < nsend || recvd < nrecv) {
-    poll.Clear();
-    if (recvd < nrecv) poll.WatchRead(from->sock.fd);
-    if (sent < nsend) poll.WatchWrite(to->sock.fd);
+    ws.Clear();
+    if (recvd < nrecv) WantRecv(&ws, from);
+    if (sent < nsend) WantSend(&ws, to);
     // a neighbour this primitive does not talk to may have died: nothing would ever wake us up, so probe
     // all links whenever nothing moved for a while
-    if (!WaitLinks(&poll)) return Status::kPeerClosed;
-    if (recvd < nrecv && poll.CheckRead(from->sock.fd)) {
+    if (!WaitLinks(&ws)) return Status::kPeerClosed;
+    if (recvd < nrecv && CanRecv(ws, from)) {
       size_t got; Status s = RecvSome(from, recv + recvd, nrecv - recvd, &got);
       if (!Ok(s)) return s;
       recvd += got;
     }
-    if (sent < nsend && poll.CheckWrite(to->sock.fd)) {
+    if (sent < nsend && CanSend(ws, to)) {
       size_t put; Status s = SendSome(to, send + sent, nsend - sent, &put);
       if (!Ok(s)) return s;
       sent += put;

@@ -21,6 +21,7 @@
 #include "config.h"
 #include "rabit/internal/engine.h"
 #include "rabit/internal/socket.h"
+#include "shm_ring.h"
 
 namespace rabit {
 namespace engine {
@@ -45,6 +46,21 @@ struct Link {
   int rank = -1;
   /*! \brief the peer has closed with bytes still unread (payload, or its bye): stop watching for the hang-up */
   bool hup_seen = false;
+  // ---- same-host data plane (shm_ring.h): payload through shared memory, the socket stays for liveness ----
+  bool shm = false;           // both ends agreed on it
+  ShmRing tx, rx;             // tx created here, rx opened from the peer
+  sockaddr_un bell;           // the peer's doorbell
+  socklen_t bell_len = 0;
+};
+
+/*! \brief what a primitive waits for in one turn of its loop: sockets, and conditions on shared-memory rings */
+struct WaitSet {
+  struct Item { Link *l; bool recv; };
+  utils::PollHelper poll;
+  std::vector<Item> shm;
+  bool ready_now = false;     // one of the ring conditions already holds
+  bool tcp = false;           // a socket is watched as well
+  void Clear() { poll.Clear(); shm.clear(); ready_now = false; tcp = false; }
 };
 
 class HostComm {
@@ -85,7 +101,7 @@ class HostComm {
    *  the primitive does not talk to ends the wait at once instead of at the next idle probe.
    * \return false when a link is dead
    */
-  bool WaitLinks(utils::PollHelper *poll);
+  bool WaitLinks(WaitSet *ws);
   /*! \brief tell the tracker this rank is done */
   void SendShutdown();
   /*! \brief log line on the tracker, or stdout without one */
@@ -128,6 +144,20 @@ class HostComm {
   utils::TCPSocket DialTracker();
   Link *FindLink(int r);
   Status RelayImpl(Link *from, Link *to, void *buf, size_t size);
+  // ---- link I/O: socket or shared-memory ring, same contract (non-blocking, "nothing yet" = 0 bytes and kOk) ----
+  void WantRecv(WaitSet *ws, Link *l);
+  void WantSend(WaitSet *ws, Link *l);
+  bool CanRecv(const WaitSet &ws, Link *l) const;
+  bool CanSend(const WaitSet &ws, Link *l) const;
+  Status RecvSome(Link *l, char *p, size_t max, size_t *got);
+  Status SendSome(Link *l, const char *p, size_t max, size_t *put);
+  void RingBell(Link *l);
+  void DropShm(Link *l);
+  void ReplaceLink(Link *l, const Link &fresh);
+  void OpenDoorbell();
+  bool NegotiateSharedMemory(Link *l, bool dialler);
+  int bell_fd_ = -1;                 // this process' doorbell (abstract unix datagram socket)
+  std::string bell_name_;
 
   std::vector<Link> links_;          // every live peer connection
   std::vector<Link *> tree_;         // subset: tree neighbours
@@ -135,6 +165,7 @@ class HostComm {
   Link *ring_prev_ = nullptr;
   Link *ring_next_ = nullptr;
   std::vector<char> scratch_;        // staging for reductions
+  std::vector<char> item_;           // one item that straddled the wrap of a shared-memory ring
   bool rank_assigned_ = false;       // the tracker has told us who we are
   bool world_known_ = false;
 };

@@ -40,6 +40,8 @@ struct Config {
                                              // smaller here so that the levels of the tree still overlap, doc/parameters.md)
   size_t reduce_ring_mincount = 256 << 10;   // elements; above this the ring is used (reference: 32 Ki; see doc/parameters.md)
   size_t reduce_buffer = 256UL << 20;        // cap of a per-link staging ring
+  size_t shm_ring = 4 << 20;                 // bytes per direction of a same-host link's shared-memory ring (0 = TCP only)
+  int shm_spin_us = 50;                      // look at the rings this long before sleeping on the doorbell
   bool tcp_no_delay = true;                  // reference default is off (Nagle stalls)
   int hadoop_mode = 0;
   // ---- robustness ----
@@ -89,7 +91,7 @@ struct Config {
       "rabit_device_oneshot_max", "rabit_device_nvls_min", "rabit_device_ll_max", "rabit_device_heap", "rabit_device_cache",
       "rabit_device_stream_min", "rabit_device_stream_chunk", "rabit_device_stream_first", "rabit_device_tune",
       "rabit_device_host_min", "rabit_device_host_chunk", "rabit_device_blob_min",
-      "rabit_world_size", "rabit_slave_port"};
+      "rabit_world_size", "rabit_slave_port", "rabit_shm_ring", "rabit_shm_spin_us"};
     return names;
   }
 
@@ -125,6 +127,8 @@ struct Config {
       reduce_ring_mincount = static_cast<size_t>(v);
     }
     else if (is("rabit_reduce_buffer")) reduce_buffer = ParseBytes(name, val);
+    else if (is("rabit_shm_ring")) shm_ring = ParseBytes(name, val);
+    else if (is("rabit_shm_spin_us")) shm_spin_us = atoi(val);
     else if (is("DMLC_WORKER_CONNECT_RETRY")) connect_retry = atoi(val);
     else if (is("rabit_bootstrap_cache")) bootstrap_cache = utils::StringToBool(val);
     else if (is("rabit_debug")) debug = utils::StringToBool(val);

@@ -21,6 +21,8 @@ struct Mixed { float lo; int hits; double total; };                         // 1
 void MixedMerge(Mixed &d, const Mixed &s) {                                 // NOLINT(*)
   d.lo = std::min(d.lo, s.lo); d.hits += s.hits; d.total += s.total;
 }
+struct Tri { float a, b, c; };                                              // 12 bytes: does not divide a power of two
+void TriMerge(Tri &d, const Tri &s) { d.a += s.a; d.b = std::max(d.b, s.b); d.c += s.c; }  // NOLINT(*)
 /*! \brief a set of small integers that grows when merged: serialised size differs from rank to rank */
 struct Bag {
   std::vector<int> items;
@@ -70,6 +72,21 @@ int main(int argc, char *argv[]) {
         }
         rabit::utils::Check(mx[i].lo == lo && mx[i].hits == hits && mx[i].total == total,
                             "[%d] mixed-lane reducer mismatch at %lu (iter %d)", me, static_cast<unsigned long>(i), it);  // NOLINT(*)
+      }
+    }
+    {
+      // items of 12 bytes straddle every power-of-two boundary of a staging or shared-memory ring
+      std::vector<Tri> tr(n);
+      for (size_t i = 0; i < n; ++i) {
+        tr[i].a = static_cast<float>((i + me) % 13); tr[i].b = static_cast<float>((i * (me + 1)) % 29); tr[i].c = 1.0f;
+      }
+      rabit::Reducer<Tri, TriMerge> red;
+      red.Allreduce(tr.data(), n);
+      for (size_t i = 0; i < n; ++i) {
+        float a = 0, b = 0;
+        for (int r = 0; r < world; ++r) { a += static_cast<float>((i + r) % 13); b = std::max(b, static_cast<float>((i * (r + 1)) % 29)); }
+        rabit::utils::Check(tr[i].a == a && tr[i].b == b && tr[i].c == static_cast<float>(world),
+                            "[%d] 12-byte reducer mismatch at %lu (iter %d)", me, static_cast<unsigned long>(i), it);  // NOLINT(*)
       }
     }
     {

@@ -15,6 +15,7 @@
 #include <vector>
 
 #include "../src/host/engine_core.h"
+#include "../src/host/shm_ring.h"
 
 using namespace rabit;          // NOLINT(*)
 using namespace rabit::engine;  // NOLINT(*)
@@ -355,6 +356,63 @@ TEST(watchdog_cancelled_by_quick_recovery) {
   EXPECT(e.HandleStatus(Status::kOk));
   std::this_thread::sleep_for(std::chrono::milliseconds(300));
   EXPECT(!e.watchdog_fired() && g_timeouts == 0);
+}
+
+// ---- shared-memory ring of same-host links (src/host/shm_ring.h) ----
+TEST(shm_ring_streams_bytes_across_the_wrap) {
+  ShmRing tx, rx;
+  EXPECT(tx.Create(64 << 10));
+  EXPECT(rx.Open(static_cast<int>(getpid()), tx.fd(), 64 << 10));   // the consumer's way in: /proc/<pid>/fd/<n>
+  EXPECT(!rx.Open(static_cast<int>(getpid()), tx.fd(), 128 << 10)); // a size that does not match is refused
+  EXPECT(rx.Open(static_cast<int>(getpid()), tx.fd(), 64 << 10));
+  EXPECT(tx.Space() == (64 << 10) && rx.Avail() == 0);
+  const size_t total = 3000000;    // ~46 laps
+  std::thread producer([&]() {
+    std::vector<char> piece(40000);
+    size_t sent = 0;
+    unsigned seed = 12345;
+    while (sent < total) {
+      seed = seed * 1103515245u + 12345u;
+      size_t n = std::min<size_t>(1 + (seed >> 8) % piece.size(), total - sent);
+      for (size_t i = 0; i < n; ++i) piece[i] = static_cast<char>((sent + i) * 31 % 251);
+      size_t off = 0;
+      while (off < n) off += tx.Write(piece.data() + off, n - off);
+      sent += n;
+    }
+  });
+  std::vector<char> out(7777);
+  size_t got = 0;
+  bool good = true;
+  unsigned seed = 999;
+  while (got < total) {
+    seed = seed * 1103515245u + 12345u;
+    if ((seed >> 10) % 3 == 0) {
+      // zero-copy path: what lies contiguously in the mapping
+      const char *span;
+      size_t n = std::min(rx.Peek(&span), total - got);
+      for (size_t i = 0; i < n; ++i) good = good && span[i] == static_cast<char>((got + i) * 31 % 251);
+      rx.Consume(n);
+      got += n;
+    } else {
+      size_t n = rx.Read(out.data(), std::min(out.size(), total - got));
+      for (size_t i = 0; i < n; ++i) good = good && out[i] == static_cast<char>((got + i) * 31 % 251);
+      got += n;
+    }
+  }
+  producer.join();
+  EXPECT(good);
+  EXPECT(rx.Avail() == 0 && tx.Space() == (64 << 10));
+  // the sleep / wake notes
+  rx.SetConsumerWaiting(1);
+  EXPECT(tx.TakeConsumerWaiting());
+  EXPECT(!tx.TakeConsumerWaiting());
+  tx.SetProducerWaiting(1);
+  EXPECT(rx.TakeProducerWaiting() && !rx.TakeProducerWaiting());
+  uint64_t a[2], b[2];
+  HostToken(a); HostToken(b);
+  EXPECT(a[0] == b[0] && a[1] == b[1] && (a[0] != 0 || a[1] != 0));
+  tx.Close(); rx.Close();
+  EXPECT(!tx.Active() && !rx.Active());
 }
 
 int main(int argc, char *argv[]) {

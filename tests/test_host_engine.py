@@ -133,11 +133,15 @@ def test_recovery_at_world_31(built):
 
 
 @pytest.mark.parametrize("extra", [[], ["rabit_reduce_ring_mincount=10"], ["rabit_reduce_ring_mincount=100000000"],
-                                   ["rabit_reduce_buffer=8", "rabit_reduce_ring_mincount=100000000"]])
+                                   ["rabit_reduce_buffer=8", "rabit_reduce_ring_mincount=100000000"],
+                                   ["rabit_reduce_ring_mincount=10", "rabit_shm_ring=64K"],
+                                   ["rabit_reduce_ring_mincount=100000000", "rabit_shm_ring=64K"],
+                                   ["rabit_reduce_ring_mincount=10", "rabit_shm_ring=0"]])
 def test_custom_reducers_across_ranks(extra):
-    """Reducer<16-byte struct> (opaque merge, declared packed sum, mixed lanes) and SerializeReducer over
-    tree and ring, world 5; the last case has a per-link buffer smaller than one element"""
-    res = run_job([bin_path("reducer_multi"), "3000"] + extra, 5)
+    """Reducer<16-byte struct> (opaque merge, declared packed sum, mixed lanes), Reducer<12-byte struct> and
+    SerializeReducer over tree and ring, world 5; the 4th case has a per-link buffer smaller than one element; then
+    shared-memory rings small enough to wrap many times (12-byte items straddle the wrap), and plain TCP"""
+    res = run_job([bin_path("reducer_multi"), "30000" if any("shm_ring" in e for e in extra) else "3000"] + extra, 5)
     assert res.ok, res.outputs
     assert res.restarts == 0
 
