@@ -66,7 +66,7 @@ def find_nvcc():
 def headers():
     hs = []
     for pat in ("include/rabit/*.h", "include/rabit/internal/*.h", "include/*.h", "src/host/*.h",
-                "src/device/*.h", "src/device/*.cuh", "src/device/*.inc"):
+                "src/device/*.h", "src/device/*.cuh", "src/device/*.inc", "test/*.h"):
         hs += glob.glob(os.path.join(ROOT, pat))
     return hs
 

@@ -22,6 +22,7 @@
 #include <sys/socket.h>
 #include <sys/types.h>
 #include <sys/un.h>
+#include <time.h>
 #include <unistd.h>
 
 #include <cstring>
@@ -66,6 +67,13 @@ struct SockAddr {
     return std::string(s);
   }
 };
+
+/*! \brief monotonic seconds (deadlines inside the socket helpers) */
+inline double NowSeconds() {
+  timespec ts;
+  clock_gettime(CLOCK_MONOTONIC, &ts);
+  return static_cast<double>(ts.tv_sec) + static_cast<double>(ts.tv_nsec) * 1e-9;
+}
 
 /*! \brief thin value-type handle over a TCP socket fd; Close() is explicit */
 class TCPSocket {
@@ -186,6 +194,33 @@ class TCPSocket {
     }
     return done;
   }
+  /*!
+   * \brief RecvAll with a deadline, for handshakes between two workers: both ends are busy with exactly this
+   *  connection, so silence means the other end is gone or wedged. Returns the bytes received (< len on
+   *  timeout, close or error). Works in blocking and non-blocking mode.
+   */
+  size_t RecvAllTimed(void *buf_, size_t len, int timeout_ms) {
+    char *buf = static_cast<char *>(buf_);
+    size_t done = 0;
+    const double t_end = NowSeconds() + timeout_ms * 1e-3;
+    while (done < len) {
+      const double left = t_end - NowSeconds();
+      if (left <= 0) return done;
+      pollfd p; p.fd = fd; p.events = POLLIN; p.revents = 0;
+      const int rc = poll(&p, 1, static_cast<int>(left * 1e3) + 1);
+      if (rc < 0 && errno == EINTR) continue;
+      if (rc <= 0) return done;
+      ssize_t n = recv(fd, buf + done, len - done, MSG_DONTWAIT);
+      if (n < 0) {
+        if (errno == EINTR || errno == EAGAIN || errno == EWOULDBLOCK) continue;
+        return done;
+      }
+      if (n == 0) return done;
+      done += static_cast<size_t>(n);
+    }
+    return done;
+  }
+  bool RecvIntTimed(int *v, int timeout_ms) { return RecvAllTimed(v, sizeof(*v), timeout_ms) == sizeof(*v); }
   // ---- tracker wire helpers ----
   bool SendInt(int v) { return SendAll(&v, sizeof(v)) == sizeof(v); }
   bool RecvInt(int *v) { return RecvAll(v, sizeof(*v)) == sizeof(*v); }

@@ -230,6 +230,11 @@ class Tracker(object):
                     if self.verbose:
                         print(msg, end="" if msg.endswith("\n") else "\n", flush=True)
                     continue
+                if c.cmd == "status":
+                    # (not part of the reference protocol) a worker parked in its accept loop asks whether the peers
+                    # it is waiting for can still turn up: once a rank has left for good, they cannot
+                    c.send_int(len(shutdown))
+                    continue
                 if c.cmd == "shutdown":
                     if c.rank >= 0:
                         shutdown.add(c.rank)

@@ -17,6 +17,8 @@ namespace engine {
 namespace {
 /*! \brief idle time after which a blocked primitive probes every link for a silent death */
 const int kProbeMs = 100;
+/*! \brief longest silence tolerated inside the dial / accept handshake of one connection (both ends are active in it) */
+const int kHandshakeMs = 15000;
 /*! \brief handshake cookie of the tracker protocol (reference allreduce_base.h kMagic) */
 const int kTrackerMagic = 0xff99;
 
@@ -87,7 +89,7 @@ bool HostComm::LinksBroken() {
 
 bool HostComm::WaitLinks(WaitSet *ws) {
   auto ring_ready = [](const WaitSet::Item &it) {
-    return it.recv ? it.l->rx.Avail() != 0 : it.l->tx.Space() >= it.l->tx.SendThreshold();
+    return it.recv ? it.l->rx.Avail() >= it.need : it.l->tx.Space() >= it.l->tx.SendThreshold();
   };
   if (!ws->ready_now && !ws->shm.empty()) {
     // a short look before going to sleep: the other end usually is a few microseconds away
@@ -105,8 +107,10 @@ bool HostComm::WaitLinks(WaitSet *ws) {
       for (const WaitSet::Item &it : ws->shm) if (ring_ready(it)) { ws->ready_now = true; break; }
     }
   }
-  // bytes are waiting in shared memory and no socket needs asking: nothing to ask the kernel
-  if (ws->ready_now && !ws->tcp) return true;
+  // bytes are waiting in shared memory and no socket needs asking: nothing to ask the kernel (but look at the
+  // sockets every so often all the same: a peer's death must not go unnoticed however busy the rings are)
+  if (ws->ready_now && !ws->tcp && ++fast_turns_ < 4096) return true;
+  fast_turns_ = 0;
   utils::PollHelper *poll = &ws->poll;
   if (!ws->shm.empty() && bell_fd_ >= 0) poll->WatchRead(bell_fd_);
   for (Link &l : links_) if (!l.hup_seen && !l.sock.IsClosed()) poll->WatchHangup(l.sock.fd);
@@ -190,15 +194,15 @@ void HostComm::DropShm(Link *l) {
   l->bell_len = 0;
 }
 
-void HostComm::WantRecv(WaitSet *ws, Link *l) {
+void HostComm::WantRecv(WaitSet *ws, Link *l, size_t need) {
   if (!l->shm) { ws->poll.WatchRead(l->sock.fd); ws->tcp = true; return; }
-  ws->shm.push_back(WaitSet::Item{l, true});
-  if (l->rx.Avail() != 0) ws->ready_now = true;
+  ws->shm.push_back(WaitSet::Item{l, true, need});
+  if (l->rx.Avail() >= need) ws->ready_now = true;
 }
 
 void HostComm::WantSend(WaitSet *ws, Link *l) {
   if (!l->shm) { ws->poll.WatchWrite(l->sock.fd); ws->tcp = true; return; }
-  ws->shm.push_back(WaitSet::Item{l, false});
+  ws->shm.push_back(WaitSet::Item{l, false, 0});
   if (l->tx.Space() >= l->tx.SendThreshold()) ws->ready_now = true;
 }
 
@@ -301,7 +305,8 @@ bool HostComm::Connect(const char *cmd) {
         // different worker by now: ephemeral ports are recycled quickly), and who answered
         int echoed = -1;
         nl.rank = peer_rank;
-        if (!nl.sock.SendInt(rank) || !nl.sock.SendInt(peer_rank) || !nl.sock.RecvInt(&echoed) || echoed != peer_rank ||
+        if (!nl.sock.SendInt(rank) || !nl.sock.SendInt(peer_rank) || !nl.sock.RecvIntTimed(&echoed, kHandshakeMs) ||
+            echoed != peer_rank ||
             !NegotiateSharedMemory(&nl, true)) {
           nl.sock.Close(); ++nerr; continue;
         }
@@ -324,16 +329,26 @@ bool HostComm::Connect(const char *cmd) {
     // A peer that died between the tracker's plan and its dial would leave us in accept() for good (the
     // reference blocks there, allreduce_base.cc:420-436); give up after a while so that the caller goes back
     // to the tracker, where the replacement process will turn up.
-    const int accept_wait_ms = 1000 * (cfg.timeout_enabled ? std::max(cfg.timeout_sec, 1) : 300);
+    const double give_up_at = utils::GetTime() + (cfg.timeout_enabled ? std::max(cfg.timeout_sec, 1) : 300);
     while (static_cast<int>(accepted.size()) < naccept) {
       utils::PollHelper incoming;
       incoming.WatchRead(listener.fd);
-      utils::Check(incoming.Poll(accept_wait_ms) != 0, "gave up waiting for %d more neighbour(s) to connect",
-                   naccept - static_cast<int>(accepted.size()));
+      if (incoming.Poll(1000) == 0) {
+        utils::Check(utils::GetTime() < give_up_at, "gave up waiting for %d more neighbour(s) to connect",
+                     naccept - static_cast<int>(accepted.size()));
+        // The peers we wait for may have finished meanwhile: the job's last barrier can complete on some ranks
+        // and break on others, and a rank that passed it leaves without looking back. They will never dial.
+        if (this->JobIsOver()) {
+          job_over = true;
+          utils::Error("the job is over: other ranks have already shut down");
+        }
+        continue;
+      }
       Link nl;
       nl.sock = listener.Accept();
       int intended = -1;
-      if (!nl.sock.SendInt(rank) || !nl.sock.RecvInt(&nl.rank) || !nl.sock.RecvInt(&intended) || intended != rank ||
+      if (!nl.sock.SendInt(rank) || !nl.sock.RecvIntTimed(&nl.rank, kHandshakeMs) ||
+          !nl.sock.RecvIntTimed(&intended, kHandshakeMs) || intended != rank ||
           std::find(expected.begin(), expected.end(), nl.rank) == expected.end() || !NegotiateSharedMemory(&nl, false)) {
         nl.sock.Close();  // dialler died, or was sent here by mistake
         continue;
@@ -426,7 +441,7 @@ bool HostComm::NegotiateSharedMemory(Link *l, bool dialler) {
   if (cfg.tcp_no_delay) l->sock.SetNoDelay(true);
   ShmHello peer;
   auto send_hello = [&]() { return l->sock.SendAll(&mine, sizeof(mine)) == sizeof(mine); };
-  auto recv_hello = [&]() { return l->sock.RecvAll(&peer, sizeof(peer)) == sizeof(peer) && peer.magic == kHelloMagic; };
+  auto recv_hello = [&]() { return l->sock.RecvAllTimed(&peer, sizeof(peer), kHandshakeMs) == sizeof(peer) && peer.magic == kHelloMagic; };
   if (dialler ? !(send_hello() && recv_hello()) : !(recv_hello() && send_hello())) { DropShm(l); return false; }
   peer.bell[sizeof(peer.bell) - 1] = '\0';
   const size_t blen = strlen(peer.bell);
@@ -440,7 +455,7 @@ bool HostComm::NegotiateSharedMemory(Link *l, bool dialler) {
     ok = 1;
   }
   auto send_ok = [&]() { return l->sock.SendAll(&ok, 1) == 1; };
-  auto recv_ok = [&]() { return l->sock.RecvAll(&peer_ok, 1) == 1; };
+  auto recv_ok = [&]() { return l->sock.RecvAllTimed(&peer_ok, 1, kHandshakeMs) == 1; };
   if (dialler ? !(send_ok() && recv_ok()) : !(recv_ok() && send_ok())) { DropShm(l); return false; }
   if (ok != 0 && peer_ok != 0) {
     l->shm = true;
@@ -448,6 +463,23 @@ bool HostComm::NegotiateSharedMemory(Link *l, bool dialler) {
     DropShm(l);
   }
   return true;
+}
+
+bool HostComm::JobIsOver() {
+  // one quiet attempt: the tracker may be busy or gone, and then the answer simply is "not known to be over"
+  utils::TCPSocket t;
+  t.Create();
+  t.SetNoDelay(true);
+  bool over = false;
+  int magic = kTrackerMagic, n = 0;
+  if (t.Connect(utils::SockAddr(cfg.tracker_uri.c_str(), cfg.tracker_port)) && t.SendInt(magic) &&
+      t.RecvIntTimed(&magic, 2000) && magic == kTrackerMagic && t.SendInt(rank_assigned_ ? rank : -1) &&
+      t.SendInt(world_known_ ? world : cfg.world_size_hint) && t.SendStr(cfg.task_id) && t.SendStr("status") &&
+      t.RecvIntTimed(&n, 2000)) {
+    over = n > 0;
+  }
+  t.Close();
+  return over;
 }
 
 void HostComm::SendShutdown() {
@@ -671,17 +703,20 @@ Status HostComm::ReduceScatterRing(void *buf_, size_t eb, size_t count, ReduceFu
   char *stage = scratch_.data();
   size_t recvd = 0, reduced = 0, sent = 0;
   const MPI::Datatype dtype(eb);
+  // between workers of one host the partial sums are folded where they lie, in the shared-memory ring
+  const bool fold_in_ring = ring_next_->shm && eb <= ring_next_->rx.capacity() / 4;
   WaitSet ws;
   while (sent < total_send || reduced < total_recv) {
     size_t sendable = std::min(total_send, head + reduced);
     ws.Clear();
     const bool can_read = recvd < total_recv && recvd - reduced < cap;
-    if (can_read) WantRecv(&ws, ring_next_);
+    // (the fold out of a shared-memory ring works on whole items: do not wake up for a part of one)
+    if (can_read) WantRecv(&ws, ring_next_, fold_in_ring ? eb : 1);
     if (sent < sendable) WantSend(&ws, ring_prev_);
     // a neighbour this primitive does not talk to may have died: nothing would ever wake us up, so probe
     // all links whenever nothing moved for a while
     if (!WaitLinks(&ws)) return Status::kPeerClosed;
-    if (can_read && ring_next_->shm) {
+    if (can_read && fold_in_ring) {
       // fold straight out of the shared-memory ring: no staging copy. One contiguous span per turn, so that the
       // partial sums it produces leave for the predecessor before the next span is folded.
       ShmRing &rx = ring_next_->rx;

@@ -55,7 +55,7 @@ struct Link {
 
 /*! \brief what a primitive waits for in one turn of its loop: sockets, and conditions on shared-memory rings */
 struct WaitSet {
-  struct Item { Link *l; bool recv; };
+  struct Item { Link *l; bool recv; size_t need; };   // recv: at least `need` unread bytes; send: room for a piece
   utils::PollHelper poll;
   std::vector<Item> shm;
   bool ready_now = false;     // one of the ring conditions already holds
@@ -102,6 +102,8 @@ class HostComm {
    * \return false when a link is dead
    */
   bool WaitLinks(WaitSet *ws);
+  /*! \brief ask the tracker (our tracker's "status" command) whether some rank has already left the job for good */
+  bool JobIsOver();
   /*! \brief tell the tracker this rank is done */
   void SendShutdown();
   /*! \brief log line on the tracker, or stdout without one */
@@ -145,7 +147,7 @@ class HostComm {
   Link *FindLink(int r);
   Status RelayImpl(Link *from, Link *to, void *buf, size_t size);
   // ---- link I/O: socket or shared-memory ring, same contract (non-blocking, "nothing yet" = 0 bytes and kOk) ----
-  void WantRecv(WaitSet *ws, Link *l);
+  void WantRecv(WaitSet *ws, Link *l, size_t need = 1);
   void WantSend(WaitSet *ws, Link *l);
   bool CanRecv(const WaitSet &ws, Link *l) const;
   bool CanSend(const WaitSet &ws, Link *l) const;
@@ -157,6 +159,7 @@ class HostComm {
   void OpenDoorbell();
   bool NegotiateSharedMemory(Link *l, bool dialler);
   int bell_fd_ = -1;                 // this process' doorbell (abstract unix datagram socket)
+  unsigned fast_turns_ = 0;          // consecutive waits answered from shared memory alone (no look at the sockets)
   std::string bell_name_;
 
   std::vector<Link> links_;          // every live peer connection

@@ -11,7 +11,9 @@
 #ifndef RABIT_TEST_RECOVER_COMMON_H_
 #define RABIT_TEST_RECOVER_COMMON_H_
 
+#include <execinfo.h>
 #include <rabit/rabit.h>
+#include <signal.h>
 
 #include <algorithm>
 #include <cmath>
@@ -21,6 +23,17 @@
 #include <vector>
 
 namespace rtest {
+
+/*! \brief post-mortem aid for the kill campaigns: RABIT_TEST_STACKDUMP=1 makes SIGUSR1 print the stack of the worker */
+inline void StackDumpHandler(int) {
+  void *frames[48];
+  const int n = backtrace(frames, 48);
+  backtrace_symbols_fd(frames, n, 2);
+}
+struct StackDumpInstaller {
+  StackDumpInstaller() { if (getenv("RABIT_TEST_STACKDUMP") != nullptr) signal(SIGUSR1, StackDumpHandler); }
+};
+static StackDumpInstaller g_stack_dump_installer;
 
 /*! \brief a vector of floats as a checkpointable model */
 struct VecModel : public rabit::Serializable {

@@ -16,7 +16,8 @@ sys.path.insert(0, ROOT)
 from rabit_b200.parallel.tracker import Tracker  # noqa: E402
 
 
-def run(seed, programs=("model_recover", "model_recover", "lazy_recover"), timeout=120, extra_args=(), tail=700):
+def run(seed, programs=("model_recover", "model_recover", "lazy_recover"), timeout=120, extra_args=(), tail=700,
+        on_stuck=None):
     rng = random.Random(seed)
     world = rng.choice([2, 3, 4, 6, 8])
     prog = rng.choice(list(programs))
@@ -41,6 +42,18 @@ def run(seed, programs=("model_recover", "model_recover", "lazy_recover"), timeo
         bindir = os.environ.get("RABIT_CHAOS_BIN", os.path.join(ROOT, "build", "bin"))   # e.g. build/san_address
         procs[i] = subprocess.Popen([os.path.join(bindir, prog)] + args, env=env,
                                     stdout=subprocess.PIPE, stderr=subprocess.STDOUT)
+        os.set_blocking(procs[i].stdout.fileno(), False)
+
+    def drain(i):
+        # keep the pipe empty: a chatty worker (rabit_debug=1) must not block on a full pipe while it is alive
+        try:
+            while True:
+                chunk = os.read(procs[i].stdout.fileno(), 1 << 16)
+                if not chunk:
+                    return
+                outs[i] += chunk
+        except (BlockingIOError, OSError, ValueError):
+            return
 
     for i in range(world):
         spawn(i)
@@ -52,10 +65,11 @@ def run(seed, programs=("model_recover", "model_recover", "lazy_recover"), timeo
         for i in range(world):
             if i in done:
                 continue
+            drain(i)
             rc = procs[i].poll()
             if rc is None:
                 continue
-            outs[i] += procs[i].stdout.read()
+            drain(i)
             if rc == 0:
                 done[i] = 0
             else:
@@ -72,13 +86,13 @@ def run(seed, programs=("model_recover", "model_recover", "lazy_recover"), timeo
                 kills.append(victim)
             next_kill = time.time() + rng.uniform(*gap)
     ok = len(done) == world and all(rc == 0 for rc in done.values())
+    if not ok and on_stuck is not None:
+        on_stuck({i: procs[i] for i in range(world) if procs[i].poll() is None}, tracker)   # post-mortem before the kill
     for i in range(world):
         if procs[i].poll() is None:
             procs[i].kill()
-        try:
-            outs[i] += procs[i].stdout.read()
-        except (OSError, ValueError):
-            pass
+        procs[i].wait()
+        drain(i)
     tracker.close()
     return ok, dict(seed=seed, world=world, prog=prog, args=args, kills=kills, done=done,
                     tails={i: outs[i].decode(errors="replace")[-tail:] for i in range(world)})

@@ -153,3 +153,45 @@ def test_replacement_worker_after_the_job_ended_exits_cleanly(built):
         assert p.returncode == 0 and "nothing to re-join" in out, out
     finally:
         t.close()
+
+
+def test_worker_parked_in_accept_learns_that_the_job_is_over(built):
+    """The job's last barrier can complete on some ranks and break on others; a rank that passed it leaves for good.
+    A worker that is then waiting for that rank to dial it asks the tracker ("status") once a second and leaves as
+    well, instead of sitting out its whole accept timeout (60 s here, 300 s by default)."""
+    import os
+    import struct
+    import subprocess
+    import time
+    from conftest import bin_path
+    from rabit_b200.parallel.tracker import Tracker, MAGIC
+
+    def hello(t, rank, task, cmd):
+        s = _raw(t)
+        s.sendall(struct.pack("@i", MAGIC))
+        assert struct.unpack("@i", s.recv(4))[0] == MAGIC
+        s.sendall(struct.pack("@iii", rank, 2, len(task)) + task + struct.pack("@i", len(cmd)) + cmd.encode())
+        return s
+
+    t = Tracker(2).start()
+    try:
+        ghost = hello(t, -1, b"0", "start")          # will be rank 0: takes its assignment, then never shows up as a peer
+        env = dict(os.environ)
+        env.update(t.worker_env())
+        env.update({"DMLC_TASK_ID": "1", "DMLC_NUM_ATTEMPT": "0", "rabit_timeout": "1", "rabit_timeout_sec": "60"})
+        t0 = time.time()
+        worker = subprocess.Popen([bin_path("basic")], env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)
+        ghost.settimeout(30)
+        ghost.recv(4096)                              # rank, parent, world, neighbours, ring
+        ghost.sendall(struct.pack("@i", 0))           # no surviving links
+        ghost.recv(8)                                 # nothing to dial, one peer will dial us
+        ghost.sendall(struct.pack("@ii", 0, 1))       # no errors; a port where nobody listens
+        ghost.close()
+        time.sleep(1.5)                               # the worker failed to reach "rank 0" and is parked in accept by now
+        hello(t, 0, b"0", "shutdown").close()         # rank 0 has left for good
+        out = worker.communicate(timeout=30)[0].decode(errors="replace")
+        assert worker.returncode == 0, out
+        assert time.time() - t0 < 20, out
+        assert "nothing to re-join" in out, out
+    finally:
+        t.close()
