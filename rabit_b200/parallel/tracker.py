@@ -10,6 +10,10 @@ unmodified reference worker binary can rendezvous here:
 * ``start`` / ``recover``: the tracker answers with rank, tree parent, world size, the
   tree neighbours and the ring neighbours, then brokers the peer connections
 * ``print``: one log line; ``shutdown``: the rank is done
+* two answers that are not part of the reference protocol (the reference's workers never see them): rank ``-2``
+  to a ``start`` / ``recover`` that arrives after some rank has shut down ("the job is over"), and the command
+  ``status`` (answer: how many ranks have shut down), which a worker waiting in ``accept()`` uses to find out that
+  the neighbours it waits for have left for good
 
 Topology: binary heap tree; the ring is a depth-first walk of that tree and ranks are
 relabelled so that the ring is simply ``r -> r + 1 (mod n)`` (the ring collectives

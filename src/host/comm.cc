@@ -88,6 +88,10 @@ bool HostComm::LinksBroken() {
 }
 
 bool HostComm::WaitLinks(WaitSet *ws) {
+  if (ws->left >= 0) {
+    snprintf(g_last_sock_what, sizeof(g_last_sock_what), "rank %d has closed its end", ws->left);
+    return false;
+  }
   auto ring_ready = [](const WaitSet::Item &it) {
     return it.recv ? it.l->rx.Avail() >= it.need : it.l->tx.Space() >= it.l->tx.SendThreshold();
   };
@@ -197,12 +201,19 @@ void HostComm::DropShm(Link *l) {
 void HostComm::WantRecv(WaitSet *ws, Link *l, size_t need) {
   if (!l->shm) { ws->poll.WatchRead(l->sock.fd); ws->tcp = true; return; }
   ws->shm.push_back(WaitSet::Item{l, true, need});
-  if (l->rx.Avail() >= need) ws->ready_now = true;
+  if (l->rx.Avail() >= need) {
+    ws->ready_now = true;
+  } else if (l->hup_seen) {
+    // The peer closed its connection (it finished and said bye, or it is re-joining) after writing all it was going
+    // to write. With payload on the socket the reader would hit the end of the stream; a ring just stays empty.
+    ws->left = l->rank;
+  }
 }
 
 void HostComm::WantSend(WaitSet *ws, Link *l) {
   if (!l->shm) { ws->poll.WatchWrite(l->sock.fd); ws->tcp = true; return; }
   ws->shm.push_back(WaitSet::Item{l, false, 0});
+  if (l->hup_seen) { ws->left = l->rank; return; }   // nobody will read it (a socket would answer with EPIPE)
   if (l->tx.Space() >= l->tx.SendThreshold()) ws->ready_now = true;
 }
 

@@ -60,7 +60,8 @@ struct WaitSet {
   std::vector<Item> shm;
   bool ready_now = false;     // one of the ring conditions already holds
   bool tcp = false;           // a socket is watched as well
-  void Clear() { poll.Clear(); shm.clear(); ready_now = false; tcp = false; }
+  int left = -1;              // a ring is waited on whose other end has closed its connection: nothing will move
+  void Clear() { poll.Clear(); shm.clear(); ready_now = false; tcp = false; left = -1; }
 };
 
 class HostComm {

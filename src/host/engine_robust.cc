@@ -71,6 +71,13 @@ bool RobustEngine::Shutdown(void) {
       return BaseEngine::Shutdown();
     }
     fprintf(stderr, "[rabit] shutdown: %s\n", e.what());
+    // This rank leaves all the same (the caller is past its last collective): say so, or the ranks that are still
+    // trying to re-join would wait for it until their timeouts.
+    StopWatchdog();
+    if (device_) { device_->Detach(); device_.reset(); }
+    comm_.CloseLinks();
+    comm_.SendShutdown();
+    initialized_ = false;
     return false;
   }
 }

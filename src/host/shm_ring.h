@@ -82,11 +82,11 @@ class ShmRing {
 
   /*! \brief bytes the consumer can take now */
   size_t Avail() const {
-    return static_cast<size_t>(hdr_->head.load(std::memory_order_acquire) - hdr_->tail.load(std::memory_order_relaxed));
+    return static_cast<size_t>(hdr_->head.load(std::memory_order_seq_cst) - hdr_->tail.load(std::memory_order_relaxed));
   }
   /*! \brief bytes the producer can put now */
   size_t Space() const {
-    return cap_ - static_cast<size_t>(hdr_->head.load(std::memory_order_relaxed) - hdr_->tail.load(std::memory_order_acquire));
+    return cap_ - static_cast<size_t>(hdr_->head.load(std::memory_order_relaxed) - hdr_->tail.load(std::memory_order_seq_cst));
   }
   /*! \brief a producer only starts a piece when this much is free: keeps the copies large when the consumer is the slower side */
   size_t SendThreshold() const { return cap_ / 4; }
@@ -136,17 +136,11 @@ class ShmRing {
   bool TakeProducerWaiting() {
     return hdr_->producer_waiting.load(std::memory_order_seq_cst) != 0 && hdr_->producer_waiting.exchange(0) != 0;
   }
-  /*! \brief "I am about to sleep": the caller MUST look at Avail() / Space() once more afterwards. The fence pairs with
-   *  the seq_cst store of head / tail on the other side: either that look sees the new bytes, or the other side sees
+  /*! \brief "I am about to sleep": the caller MUST look at Avail() / Space() once more afterwards. Note, look (here) and
+   *  publish, read the note (other side) are all seq_cst: either that look sees the new bytes, or the other side sees
    *  the note and rings the doorbell. */
-  void SetConsumerWaiting(uint32_t v) {
-    hdr_->consumer_waiting.store(v, std::memory_order_seq_cst);
-    std::atomic_thread_fence(std::memory_order_seq_cst);
-  }
-  void SetProducerWaiting(uint32_t v) {
-    hdr_->producer_waiting.store(v, std::memory_order_seq_cst);
-    std::atomic_thread_fence(std::memory_order_seq_cst);
-  }
+  void SetConsumerWaiting(uint32_t v) { hdr_->consumer_waiting.store(v, std::memory_order_seq_cst); }
+  void SetProducerWaiting(uint32_t v) { hdr_->producer_waiting.store(v, std::memory_order_seq_cst); }
 
  private:
   bool Map(size_t bytes) {

@@ -157,3 +157,31 @@ def test_tree_reduce_minsize_small_and_large():
         res = run_job([bin_path("model_recover"), "30000", "rabit_reduce_ring_mincount=100000000",
                        "rabit_tree_reduce_minsize=" + v], 6)
         assert res.ok, res.outputs
+
+
+@pytest.mark.parametrize("ring", ["4M", "0"])
+def test_waiting_for_a_peer_that_has_left_fails_instead_of_hanging(ring):
+    """Rank 1 finishes and says bye; rank 0 then starts one more collective that needs rank 1. With the payload on the
+    socket the reader hits the end of the stream; a shared-memory ring just stays empty, so the wait must notice that
+    the peer's connection is closed (found by the kill campaigns: a re-run shutdown barrier waiting for ranks that
+    had already passed it)."""
+    import time
+    from conftest import run_py
+    code = (
+        "import sys, time, numpy as np\n"
+        "from rabit_b200 import rabit\n"
+        "rabit.init(sys.argv[1:], lib='base')\n"
+        "r = rabit.get_rank()\n"
+        "rabit.allreduce(np.ones(4, dtype=np.float32), rabit.SUM)\n"
+        "if r == 0:\n"
+        "    time.sleep(1.0)\n"
+        "    print('extra op starts', flush=True)\n"
+        "    rabit.allreduce(np.ones(4, dtype=np.float32), rabit.SUM)\n"
+        "    print('extra op returned', flush=True)\n"
+        "rabit.finalize()\n")
+    t0 = time.time()
+    res = run_py(code, 2, args=["rabit_shm_ring=" + ring], timeout=60, max_attempts=1)
+    assert time.time() - t0 < 30, res.outputs
+    out = "".join(res.outputs.values())     # (rabit rank 0 is whichever task the tracker labelled 0)
+    assert "extra op starts" in out and "extra op returned" not in out, res.outputs
+    assert "peer-closed" in out, res.outputs
