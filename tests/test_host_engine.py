@@ -159,7 +159,7 @@ def test_tree_reduce_minsize_small_and_large():
         assert res.ok, res.outputs
 
 
-@pytest.mark.parametrize("ring", ["4M", "0"])
+@pytest.mark.parametrize("ring", ["512K", "0"])
 def test_waiting_for_a_peer_that_has_left_fails_instead_of_hanging(ring):
     """Rank 1 finishes and says bye; rank 0 then starts one more collective that needs rank 1. With the payload on the
     socket the reader hits the end of the stream; a shared-memory ring just stays empty, so the wait must notice that
