@@ -20,3 +20,10 @@ def test_random_sigkills_device_side(built, seed):
     ok, info = run(seed, ("model_recover", "lazy_recover", "local_recover"),
                    extra_args=["rabit_device=fake", "rabit_device_host_min=1", "rabit_device_blob_min=1"])
     assert ok, {k: info[k] for k in ("prog", "world", "args", "kills", "done", "tails")}
+
+
+@pytest.mark.parametrize("seed", [3, 1007, 4219])
+def test_random_sigkills_sockets_only(built, seed):
+    """the transport between hosts: no shared-memory rings, every byte on the sockets"""
+    ok, info = run(seed, extra_args=["rabit_shm_ring=0"])
+    assert ok, {k: info[k] for k in ("prog", "world", "args", "kills", "done", "tails")}
