@@ -726,14 +726,15 @@ def ref_run(exe, argv, rank, world, store, tag, timeout=3000, env_extra=None):
 def same_program_on_this_library(rank, world, local, store, nbytes, steps):
     """baseline/ref_speed.cc, the harness of the reference arm, compiled UNCHANGED against this library
     (build/bin/ours_speed): host buffers in, host buffers out (pageable std::vector), wall clock inside the program,
-    max over ranks: what a user of the reference gets by re-linking. Once with the device backend off (host engine
-    over loopback TCP, like the reference) and once with it on (the host buffers ride the GPUs: H2D | kernels | D2H)."""
+    max over ranks: what a user of the reference gets by re-linking. Once with the device backend off (host engine:
+    sockets for rendezvous and liveness, payload through shared-memory rings between the workers of one box) and once
+    with it on (the host buffers ride the GPUs: H2D | kernels | D2H)."""
     exe = os.path.join(ROOT, "build", "bin", "ours_speed")
     if not os.path.isfile(exe):
         return {"error": "build/bin/ours_speed missing"} if rank == 0 else None
     out = {"program": "baseline/ref_speed.cc (unchanged) linked with lib/librabit_mock.so, rabit_engine=robust",
            "steps": steps, "bytes_per_rank": nbytes}
-    for tag, extra in (("host_tcp", ["rabit_device=off"]), ("via_gpus", ["rabit_device=on"])):
+    for tag, extra in (("host_engine", ["rabit_device=off"]), ("via_gpus", ["rabit_device=on"])):
         lines = ref_run(exe, [str(nbytes // 4), str(steps), "1", "rabit_engine=robust", "rabit_enable_tcp_no_delay=true"] + extra,
                         rank, world, store, "same_" + tag, timeout=240, env_extra={"RABIT_DEVICE_ORDINAL": str(local)})
         if rank == 0:

@@ -64,10 +64,10 @@ def main():
                   " standby workers, %s s without; reference (host only, no CUDA context): %s s"
                   % (f(rec.get("recover_s_per_kill"), 3), f(cold.get("recover_s_per_kill"), 3), f(rr.get("recover_s_per_kill"), 3)))
         sp = d.get("same_program") or {}
-        if sp.get("host_tcp") or sp.get("via_gpus"):
+        if sp.get("host_engine") or sp.get("via_gpus"):
             print("* the reference arm's harness (`baseline/ref_speed.cc`, unchanged) linked with this library, host buffers in and out: "
-                  "%s ms/step over loopback TCP (device backend off), %s ms/step with the host buffers riding the GPUs%s"
-                  % (f((sp.get("host_tcp") or {}).get("ms_per_step"), 1), f((sp.get("via_gpus") or {}).get("ms_per_step"), 1),
+                  "%s ms/step on the host engine (device backend off), %s ms/step with the host buffers riding the GPUs%s"
+                  % (f((sp.get("host_engine") or {}).get("ms_per_step"), 1), f((sp.get("via_gpus") or {}).get("ms_per_step"), 1),
                      ("; the reference itself: %s ms/step" % f(r["ms_per_step"], 0)) if r else ""))
         sc = d.get("selfcheck") or {}
         print("* bit-exact self-check on these ranks: %s cases, failed: %s; kernels launched in the timed region: %s; clocks %s"

@@ -225,6 +225,11 @@ bool HostComm::CanSend(const WaitSet &ws, Link *l) const {
   return l->shm ? l->tx.Space() >= l->tx.SendThreshold() : ws.poll.CheckWrite(l->sock.fd);
 }
 
+bool HostComm::AllLinksSharedMemory() const {
+  for (const Link &l : links_) if (!l.shm) return false;
+  return !links_.empty();
+}
+
 Link *HostComm::FindLink(int r) {
   for (Link &l : links_) if (l.rank == r) return &l;
   return nullptr;
@@ -515,7 +520,7 @@ void HostComm::TrackerPrint(const std::string &msg) {
 // -------------------------------------------------------------- collectives
 Status HostComm::Allreduce(void *buf, size_t elem_bytes, size_t count, ReduceFunction *reducer) {
   if (world <= 1 || count == 0) return Status::kOk;
-  if (count > cfg.reduce_ring_mincount) return AllreduceRing(buf, elem_bytes, count, reducer);
+  if (UseRing(elem_bytes, count)) return AllreduceRing(buf, elem_bytes, count, reducer);
   return AllreduceTree(buf, elem_bytes, count, reducer);
 }
 
@@ -786,7 +791,7 @@ Status HostComm::ReduceScatterRing(void *buf_, size_t eb, size_t count, ReduceFu
 
 Status HostComm::AllreduceFrom(const void *src, void *dst, size_t eb, size_t count, ReduceFunction *reducer) {
   if (count == 0) return Status::kOk;
-  if (world <= 1 || count <= cfg.reduce_ring_mincount || src == dst) {
+  if (world <= 1 || !UseRing(eb, count) || src == dst) {
     if (src != dst) std::memcpy(dst, src, eb * count);
     return Allreduce(dst, eb, count, reducer);
   }

@@ -85,6 +85,19 @@ class HostComm {
   bool job_over = false;
 
   bool distributed() const { return cfg.tracker_uri != "NULL"; }
+  /*! \brief every link of THIS rank carries its payload through shared memory */
+  bool AllLinksSharedMemory() const;
+  /*!
+   * \brief agreed by all ranks after a rendezvous (BaseEngine::AttachDevice): every link of the job is shared memory.
+   *  The ring then beats the tree from 32 KiB (measured, profiles/r2_host_engine_cpu.md) instead of from
+   *  rabit_reduce_ring_mincount elements; the choice must be the same on every rank, hence the agreement.
+   */
+  bool shm_everywhere = false;
+  /*! \brief tree or ring for an allreduce of count items of elem_bytes */
+  bool UseRing(size_t elem_bytes, size_t count) const {
+    if (shm_everywhere && !cfg.reduce_ring_mincount_set) return elem_bytes * count >= (32u << 10);
+    return count > cfg.reduce_ring_mincount;
+  }
 
   // ---- rendezvous ----
   /*! \brief talk to the tracker with cmd "start" or "recover" and (re)build every link */

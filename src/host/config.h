@@ -39,6 +39,7 @@ struct Config {
   size_t tree_reduce_minsize = 64 << 10;     // bytes a tree node gathers before it folds and forwards (reference: 1 MiB;
                                              // smaller here so that the levels of the tree still overlap, doc/parameters.md)
   size_t reduce_ring_mincount = 256 << 10;   // elements; above this the ring is used (reference: 32 Ki; see doc/parameters.md)
+  bool reduce_ring_mincount_set = false;     // given by the user: then it also holds when every link is shared memory
   size_t reduce_buffer = 256UL << 20;        // cap of a per-link staging ring
   size_t shm_ring = 512 << 10;               // bytes per direction of a same-host link's shared-memory ring (0 = TCP only);
                                              // measured: a ring that stays in the L2 beats a large one at every message size
@@ -126,6 +127,7 @@ struct Config {
       long v = atol(val);  // NOLINT(*)
       utils::Check(v >= 0, "rabit_reduce_ring_mincount should be non-negative");
       reduce_ring_mincount = static_cast<size_t>(v);
+      reduce_ring_mincount_set = true;
     }
     else if (is("rabit_reduce_buffer")) reduce_buffer = ParseBytes(name, val);
     else if (is("rabit_shm_ring")) shm_ring = ParseBytes(name, val);

@@ -97,15 +97,20 @@ BaseEngine::AttachResult BaseEngine::AttachDevice() {
   // visible, wrong architecture, rabit_device=off only there) must not skip the bootstrap while the others run
   // its host collectives: the byte streams of different collectives would be paired. So everybody takes part in
   // this agreement, with or without a backend, after every rendezvous.
-  int have = device_ ? 1 : 0;
+  int agreed[2] = {device_ ? 1 : 0, comm_.AllLinksSharedMemory() ? 1 : 0};
   if (comm_.world > 1) {
-    const Status st = comm_.Allreduce(&have, sizeof(int), 1, [](const void *s, void *d, int n, const MPI::Datatype &) {
+    // (the second value rides along: do all links of the job carry their payload through shared memory? The choice
+    // between tree and ring depends on it and has to be the same everywhere, HostComm::UseRing)
+    comm_.shm_everywhere = false;
+    const Status st = comm_.Allreduce(agreed, sizeof(int), 2, [](const void *s, void *d, int n, const MPI::Datatype &) {
       const int *src = static_cast<const int *>(s);
       int *dst = static_cast<int *>(d);
       for (int i = 0; i < n; ++i) dst[i] = std::min(dst[i], src[i]);
     });
     if (!Ok(st)) return AttachResult::kLinkError;
+    comm_.shm_everywhere = agreed[1] != 0;
   }
+  const int have = agreed[0];
   if (have == 0) {
     if (device_) {
       utils::Check(comm_.cfg.device != "on", "rabit_device=on but another rank has no usable GPU");
