@@ -95,7 +95,9 @@ class HostComm {
   bool shm_everywhere = false;
   /*! \brief tree or ring for an allreduce of count items of elem_bytes */
   bool UseRing(size_t elem_bytes, size_t count) const {
-    if (shm_everywhere && !cfg.reduce_ring_mincount_set) return elem_bytes * count >= (32u << 10);
+    if (shm_everywhere && !cfg.reduce_ring_mincount_set) {
+      return elem_bytes * count >= (32u << 10) && count >= static_cast<size_t>(world);
+    }
     return count > cfg.reduce_ring_mincount;
   }
 
