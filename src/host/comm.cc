@@ -449,6 +449,7 @@ bool HostComm::NegotiateSharedMemory(Link *l, bool dialler) {
   ShmHello mine; std::memset(&mine, 0, sizeof(mine));
   mine.magic = kHelloMagic;
   HostToken(mine.token);
+  if (cfg.shm_test_split > 1) mine.token[1] ^= static_cast<uint64_t>(rank % cfg.shm_test_split) + 1;  // tests: a mix of media
   mine.pid = static_cast<int32_t>(getpid());
   mine.capacity = capacity;
   snprintf(mine.bell, sizeof(mine.bell), "%s", bell_name_.c_str());

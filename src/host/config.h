@@ -44,6 +44,7 @@ struct Config {
   size_t shm_ring = 512 << 10;               // bytes per direction of a same-host link's shared-memory ring (0 = TCP only);
                                              // measured: a ring that stays in the L2 beats a large one at every message size
   int shm_spin_us = 50;                      // look at the rings this long before sleeping on the doorbell
+  int shm_test_split = 0;                    // test hook: ranks of different (rank % split) pretend to be on different hosts
   bool tcp_no_delay = true;                  // reference default is off (Nagle stalls)
   int hadoop_mode = 0;
   // ---- robustness ----
@@ -93,7 +94,7 @@ struct Config {
       "rabit_device_oneshot_max", "rabit_device_nvls_min", "rabit_device_ll_max", "rabit_device_heap", "rabit_device_cache",
       "rabit_device_stream_min", "rabit_device_stream_chunk", "rabit_device_stream_first", "rabit_device_tune",
       "rabit_device_host_min", "rabit_device_host_chunk", "rabit_device_blob_min",
-      "rabit_world_size", "rabit_slave_port", "rabit_shm_ring", "rabit_shm_spin_us"};
+      "rabit_world_size", "rabit_slave_port", "rabit_shm_ring", "rabit_shm_spin_us", "rabit_shm_test_split"};
     return names;
   }
 
@@ -132,6 +133,7 @@ struct Config {
     else if (is("rabit_reduce_buffer")) reduce_buffer = ParseBytes(name, val);
     else if (is("rabit_shm_ring")) shm_ring = ParseBytes(name, val);
     else if (is("rabit_shm_spin_us")) shm_spin_us = atoi(val);
+    else if (is("rabit_shm_test_split")) shm_test_split = atoi(val);
     else if (is("DMLC_WORKER_CONNECT_RETRY")) connect_retry = atoi(val);
     else if (is("rabit_bootstrap_cache")) bootstrap_cache = utils::StringToBool(val);
     else if (is("rabit_debug")) debug = utils::StringToBool(val);

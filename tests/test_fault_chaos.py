@@ -27,3 +27,11 @@ def test_random_sigkills_sockets_only(built, seed):
     """the transport between hosts: no shared-memory rings, every byte on the sockets"""
     ok, info = run(seed, extra_args=["rabit_shm_ring=0"])
     assert ok, {k: info[k] for k in ("prog", "world", "args", "kills", "done", "tails")}
+
+
+@pytest.mark.parametrize("seed", [11, 393, 2043, 8559])
+def test_random_sigkills_mixed_media(built, seed):
+    """several hosts with several workers each: some links are shared-memory rings, some are sockets (test hook:
+    ranks of different parity pretend to be on different hosts)"""
+    ok, info = run(seed, extra_args=["rabit_shm_test_split=2"])
+    assert ok, {k: info[k] for k in ("prog", "world", "args", "kills", "done", "tails")}

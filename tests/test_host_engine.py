@@ -49,7 +49,8 @@ def test_model_recover_no_fault(world):
     assert res.restarts == 0
 
 
-@pytest.mark.parametrize("extra", [["rabit_shm_ring=0"], ["rabit_shm_ring=64K", "rabit_shm_spin_us=0"]])
+@pytest.mark.parametrize("extra", [["rabit_shm_ring=0"], ["rabit_shm_ring=64K", "rabit_shm_spin_us=0"],
+                                   ["rabit_shm_test_split=2"], ["rabit_shm_test_split=3", "rabit_shm_ring=64K"]])
 def test_transport_variants_no_fault(extra):
     """plain sockets, and tiny shared-memory rings (every message wraps them many times) without the look before sleeping"""
     res = run_job([bin_path("model_recover"), "300000"] + extra, 5)
@@ -92,13 +93,16 @@ SCENARIOS = {
 }
 
 
-@pytest.mark.parametrize("transport", ["shm", "tcp"])
+@pytest.mark.parametrize("transport", ["shm", "tcp", "mixed"])
 @pytest.mark.parametrize("name", sorted(SCENARIOS))
 def test_fault_matrix_world10(name, transport):
     """the reference's test/test.mk matrix at world 10; once with the payload in shared-memory rings (what workers of one
     host do by default) and once on the sockets alone (what workers of different hosts do)"""
     prog, args, deaths = SCENARIOS[name]
-    res = run_job([bin_path(prog), "10000"] + args + (["rabit_shm_ring=0"] if transport == "tcp" else []), 10, timeout=180)
+    # "mixed": ranks of different parity pretend to sit on different hosts, so that one wait covers rings AND sockets
+    # (several hosts with several workers each)
+    more = {"shm": [], "tcp": ["rabit_shm_ring=0"], "mixed": ["rabit_shm_test_split=2"]}[transport]
+    res = run_job([bin_path(prog), "10000"] + args + more, 10, timeout=180)
     assert res.ok, {i: o[-600:] for i, o in res.outputs.items()}
     assert res.restarts == deaths
     hits = sum(len(re.findall("terminate called", o)) for o in res.outputs.values())
