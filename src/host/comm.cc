@@ -483,16 +483,17 @@ bool HostComm::NegotiateSharedMemory(Link *l, bool dialler) {
 }
 
 bool HostComm::JobIsOver() {
-  // one quiet attempt: the tracker may be busy or gone, and then the answer simply is "not known to be over"
+  // one quiet attempt: the tracker may be busy (it serves one rendezvous at a time, and that worker may be dialling
+  // US right now: do not keep it waiting) or gone, and then the answer simply is "not known to be over"
   utils::TCPSocket t;
   t.Create();
   t.SetNoDelay(true);
   bool over = false;
   int magic = kTrackerMagic, n = 0;
   if (t.Connect(utils::SockAddr(cfg.tracker_uri.c_str(), cfg.tracker_port)) && t.SendInt(magic) &&
-      t.RecvIntTimed(&magic, 2000) && magic == kTrackerMagic && t.SendInt(rank_assigned_ ? rank : -1) &&
+      t.RecvIntTimed(&magic, 500) && magic == kTrackerMagic && t.SendInt(rank_assigned_ ? rank : -1) &&
       t.SendInt(world_known_ ? world : cfg.world_size_hint) && t.SendStr(cfg.task_id) && t.SendStr("status") &&
-      t.RecvIntTimed(&n, 2000)) {
+      t.RecvIntTimed(&n, 500)) {
     over = n > 0;
   }
   t.Close();
