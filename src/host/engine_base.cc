@@ -7,6 +7,8 @@
 #include "../device/device_backend.h"
 #include "engine_core.h"
 
+#include <dirent.h>
+
 namespace rabit {
 namespace engine {
 
@@ -131,6 +133,15 @@ bool BaseEngine::Shutdown(void) {
   if (device_) { device_->Detach(); device_.reset(); }
   comm_.CloseLinks(true);
   comm_.SendShutdown();
+  if (comm_.cfg.debug) {
+    // (every re-join opens sockets and shared-memory rings: this line is how the kill campaigns watch for leaks)
+    int nfd = 0;
+    if (DIR *d = opendir("/proc/self/fd")) {
+      while (readdir(d) != nullptr) ++nfd;
+      closedir(d);
+    }
+    utils::HandleLogInfo("[%d] open file descriptors after shutdown: %d\n", comm_.rank, nfd - 3);  // ".", "..", the DIR itself
+  }
   initialized_ = false;
   return true;
 }
