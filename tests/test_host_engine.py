@@ -201,3 +201,14 @@ def test_waiting_for_a_peer_that_has_left_fails_instead_of_hanging(ring):
     out = "".join(res.outputs.values())     # (rabit rank 0 is whichever task the tracker labelled 0)
     assert "extra op starts" in out and "extra op returned" not in out, res.outputs
     assert "peer-closed" in out, res.outputs
+
+
+def test_rejoins_do_not_leak_file_descriptors():
+    """every re-join opens sockets and shared-memory rings; after shutdown only stdin / stdout / stderr and the doorbell
+    socket may be left, however many re-joins there were"""
+    res = run_job([bin_path("model_recover"), "1000", "rabit_debug=1", "rabit_bootstrap_cache=1", "mock=0,0,1,0", "mock=1,1,1,0",
+                   "mock=2,1,2,0", "mock=3,2,1,0", "mock=0,2,1,1"], 4)
+    assert res.ok, res.outputs
+    assert res.restarts == 5
+    counts = re.findall(r"open file descriptors after shutdown: (\d+)", "".join(res.outputs.values()))
+    assert len(counts) == 4 and all(int(c) <= 4 for c in counts), counts
