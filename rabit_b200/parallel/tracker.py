@@ -12,8 +12,9 @@ unmodified reference worker binary can rendezvous here:
 * ``print``: one log line; ``shutdown``: the rank is done
 * two answers that are not part of the reference protocol (the reference's workers never see them): rank ``-2``
   to a ``start`` / ``recover`` that arrives after some rank has shut down ("the job is over"), and the command
-  ``status`` (answer: how many ranks have shut down), which a worker waiting in ``accept()`` uses to find out that
-  the neighbours it waits for have left for good
+  ``status`` (answer: how many ranks have shut down, and whether the asking worker is still on the list of parked
+  workers), which a worker waiting in ``accept()`` uses to find out that the neighbours it waits for have left for
+  good or will never be sent its way
 
 Topology: binary heap tree; the ring is a depth-first walk of that tree and ranks are
 relabelled so that the ring is simply ``r -> r + 1 (mod n)`` (the ring collectives
@@ -238,6 +239,9 @@ class Tracker(object):
                     # (not part of the reference protocol) a worker parked in its accept loop asks whether the peers
                     # it is waiting for can still turn up: once a rank has left for good, they cannot
                     c.send_int(len(shutdown))
+                    # ... and whether the tracker still has it on the list of workers that somebody will be sent to
+                    # dial (0 while it waits in accept(): both sides lost track of each other, it had better re-join)
+                    c.send_int(1 if c.rank in wait_conn else 0)
                     continue
                 if c.cmd == "shutdown":
                     if c.rank >= 0:

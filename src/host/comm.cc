@@ -346,6 +346,7 @@ bool HostComm::Connect(const char *cmd) {
     // reference blocks there, allreduce_base.cc:420-436); give up after a while so that the caller goes back
     // to the tracker, where the replacement process will turn up.
     const double give_up_at = utils::GetTime() + (cfg.timeout_enabled ? std::max(cfg.timeout_sec, 1) : 300);
+    int not_listed = 0;
     while (static_cast<int>(accepted.size()) < naccept) {
       utils::PollHelper incoming;
       incoming.WatchRead(listener.fd);
@@ -354,10 +355,16 @@ bool HostComm::Connect(const char *cmd) {
                      naccept - static_cast<int>(accepted.size()));
         // The peers we wait for may have finished meanwhile: the job's last barrier can complete on some ranks
         // and break on others, and a rank that passed it leaves without looking back. They will never dial.
-        if (this->JobIsOver()) {
+        bool parked = true;
+        if (this->JobIsOver(&parked)) {
           job_over = true;
           utils::Error("the job is over: other ranks have already shut down");
         }
+        // The tracker sends diallers to the workers on its list. If this worker is not on it (twice in a row: the
+        // last dialler may just be in its handshake with us) nobody will ever come: start over rather than sit
+        // out the whole timeout. (It forgets a parked worker when somebody could not reach it, taking it for dead.)
+        not_listed = parked ? 0 : not_listed + 1;
+        utils::Check(not_listed < 2, "the tracker no longer sends anybody to dial this worker; starting the rendezvous over");
         continue;
       }
       Link nl;
@@ -482,7 +489,8 @@ bool HostComm::NegotiateSharedMemory(Link *l, bool dialler) {
   return true;
 }
 
-bool HostComm::JobIsOver() {
+bool HostComm::JobIsOver(bool *parked) {
+  if (parked != nullptr) *parked = true;
   // one quiet attempt: the tracker may be busy (it serves one rendezvous at a time, and that worker may be dialling
   // US right now: do not keep it waiting) or gone, and then the answer simply is "not known to be over"
   utils::TCPSocket t;
@@ -495,6 +503,8 @@ bool HostComm::JobIsOver() {
       t.SendInt(world_known_ ? world : cfg.world_size_hint) && t.SendStr(cfg.task_id) && t.SendStr("status") &&
       t.RecvIntTimed(&n, 500)) {
     over = n > 0;
+    int listed = 1;
+    if (parked != nullptr && t.RecvIntTimed(&listed, 500)) *parked = listed != 0;
   }
   t.Close();
   return over;

@@ -118,8 +118,9 @@ class HostComm {
    * \return false when a link is dead
    */
   bool WaitLinks(WaitSet *ws);
-  /*! \brief ask the tracker (our tracker's "status" command) whether some rank has already left the job for good */
-  bool JobIsOver();
+  /*! \brief ask the tracker (our tracker's "status" command) whether some rank has already left the job for good;
+   *  *parked: whether the tracker still lists this worker as waiting for diallers */
+  bool JobIsOver(bool *parked = nullptr);
   /*! \brief tell the tracker this rank is done */
   void SendShutdown();
   /*! \brief log line on the tracker, or stdout without one */

@@ -195,3 +195,53 @@ def test_worker_parked_in_accept_learns_that_the_job_is_over(built):
         assert "nothing to re-join" in out, out
     finally:
         t.close()
+
+
+def test_worker_the_tracker_forgot_starts_over(built):
+    """The tracker drops a parked worker from its list when somebody could not reach it (it takes it for dead). If the
+    worker is alive it would wait in accept() for diallers that are never sent: `status` tells it, and it starts the
+    rendezvous over within seconds instead of sitting out its accept timeout (60 s here)."""
+    import os
+    import struct
+    import subprocess
+    import time
+    from conftest import bin_path
+    from rabit_b200.parallel.tracker import Tracker, MAGIC
+
+    def hello(t, rank, task, cmd):
+        s = _raw(t)
+        s.settimeout(30)
+        s.sendall(struct.pack("@i", MAGIC))
+        assert struct.unpack("@i", s.recv(4))[0] == MAGIC
+        s.sendall(struct.pack("@iii", rank, 2, len(task)) + task + struct.pack("@i", len(cmd)) + cmd.encode())
+        return s
+
+    t = Tracker(2).start()
+    try:
+        ghost = hello(t, -1, b"0", "start")           # rank 0; gives a port where nobody listens
+        env = dict(os.environ)
+        env.update(t.worker_env())
+        env.update({"DMLC_TASK_ID": "1", "DMLC_NUM_ATTEMPT": "0", "rabit_timeout": "1", "rabit_timeout_sec": "60"})
+        t0 = time.time()
+        worker = subprocess.Popen([bin_path("basic")], env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)
+        ghost.recv(4096)
+        ghost.sendall(struct.pack("@i", 0))
+        ghost.recv(8)
+        ghost.sendall(struct.pack("@ii", 0, 1))
+        ghost.close()
+        time.sleep(1.0)                               # the worker could not reach "rank 0" and is parked in accept
+        again = hello(t, 0, b"0", "recover")          # "rank 0" comes back, is pointed at the worker ...
+        again.recv(4096)
+        again.sendall(struct.pack("@i", 0))
+        again.recv(4096)                              # ... (its address) ...
+        again.sendall(struct.pack("@i", 1))           # ... and claims it could not reach it: the tracker forgets the worker
+        again.sendall(struct.pack("@i", 0))           # next round of the link plan: still no links
+        again.recv(8)                                 # nobody to dial any more, one peer is to dial us
+        again.sendall(struct.pack("@ii", 0, 2))
+        again.close()
+        out = worker.communicate(timeout=30)[0].decode(errors="replace")
+        assert time.time() - t0 < 20, out
+        assert "no longer sends anybody" in out, out
+        assert worker.returncode != 0, out            # Init could not join: the launcher starts the worker again
+    finally:
+        t.close()
