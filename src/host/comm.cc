@@ -10,6 +10,7 @@
 #include <cerrno>
 #include <cstddef>
 #include <map>
+#include <thread>
 
 namespace rabit {
 namespace engine {
@@ -97,8 +98,8 @@ bool HostComm::WaitLinks(WaitSet *ws) {
   };
   if (!ws->ready_now && !ws->shm.empty()) {
     // a short look before going to sleep: the other end usually is a few microseconds away
-    if (cfg.shm_spin_us > 0) {
-      const double until = utils::GetTime() + cfg.shm_spin_us * 1e-6;
+    if (spin_us_ > 0) {
+      const double until = utils::GetTime() + spin_us_ * 1e-6;
       do {
         for (const WaitSet::Item &it : ws->shm) if (ring_ready(it)) { ws->ready_now = true; break; }
       } while (!ws->ready_now && utils::GetTime() < until);
@@ -275,6 +276,11 @@ bool HostComm::Connect(const char *cmd) {
     utils::Check(new_rank >= 0, "tracker refused to assign a rank");
     utils::Assert(!rank_assigned_ || new_rank == rank, "tracker changed our rank from %d to %d", rank, new_rank);
     rank = new_rank; rank_assigned_ = true; world_known_ = true;
+    // looking at the rings before sleeping only pays while every worker has a core to itself: with more workers than
+    // cores (measured: 31 workers on 8 cores, 0.14-0.19 s without vs 0.19-0.40 s with) the one we wait for may be the
+    // one we keep off the CPU
+    const int cores = static_cast<int>(std::thread::hardware_concurrency());
+    spin_us_ = (cfg.shm_spin_set || cores <= 0 || world <= cores) ? cfg.shm_spin_us : 0;
     std::vector<int> tree_nbrs;
     utils::Check(t.RecvInt(&nnbr), "tracker: cannot read neighbour count");
     for (int i = 0; i < nnbr; ++i) {

@@ -176,7 +176,8 @@ class HostComm {
   void OpenDoorbell();
   bool NegotiateSharedMemory(Link *l, bool dialler);
   int bell_fd_ = -1;                 // this process' doorbell (abstract unix datagram socket)
-  unsigned fast_turns_ = 0;          // consecutive waits answered from shared memory alone (no look at the sockets)
+int spin_us_ = 0;                  // effective rabit_shm_spin_us (0 when the workers outnumber the cores)
+    unsigned fast_turns_ = 0;          // consecutive waits answered from shared memory alone (no look at the sockets)
   std::string bell_name_;
 
   std::vector<Link> links_;          // every live peer connection

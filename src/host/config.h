@@ -44,6 +44,7 @@ struct Config {
   size_t shm_ring = 512 << 10;               // bytes per direction of a same-host link's shared-memory ring (0 = TCP only);
                                              // measured: a ring that stays in the L2 beats a large one at every message size
   int shm_spin_us = 50;                      // look at the rings this long before sleeping on the doorbell
+  bool shm_spin_set = false;                 // given by the user: then it also holds when the workers outnumber the cores
   int shm_test_split = 0;                    // test hook: ranks of different (rank % split) pretend to be on different hosts
   bool tcp_no_delay = true;                  // reference default is off (Nagle stalls)
   int hadoop_mode = 0;
@@ -132,7 +133,7 @@ struct Config {
     }
     else if (is("rabit_reduce_buffer")) reduce_buffer = ParseBytes(name, val);
     else if (is("rabit_shm_ring")) shm_ring = ParseBytes(name, val);
-    else if (is("rabit_shm_spin_us")) shm_spin_us = atoi(val);
+    else if (is("rabit_shm_spin_us")) { shm_spin_us = atoi(val); shm_spin_set = true; }
     else if (is("rabit_shm_test_split")) shm_test_split = atoi(val);
     else if (is("DMLC_WORKER_CONNECT_RETRY")) connect_retry = atoi(val);
     else if (is("rabit_bootstrap_cache")) bootstrap_cache = utils::StringToBool(val);
